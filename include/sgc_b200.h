@@ -1,0 +1,176 @@
+/*
+ * sgc_b200.h -- C ABI of libsgc_b200.so: the B200 (sm_100a) implementation of SGC's
+ * feature-propagation hot path.
+ *
+ * What this boundary replaces.  The reference (bellaj09/SGC) is pure Python; the arithmetic
+ * of its hot path is reached through two third-party interfaces.  Every entry point below
+ * names the reference call site whose work it takes over (paths relative to the reference
+ * root):
+ *
+ *   normalization.py:5-12   aug_normalized_adjacency   -> sgc_csr_* / sgc_degree_* / sgc_norm_*
+ *   utils.py:23-30          sparse_mx_to_torch_sparse_tensor -> sgc_norm_build (fp32 view), sgc_csr_to_coo
+ *   utils.py:92-97          sgc_precompute (K x torch.spmm) -> sgc_spmm_plan_* / sgc_spmm_hop / sgc_precompute
+ *   utils.py:118-119        Reddit feature standardisation   -> sgc_col_stats (+ fused into sgc_spmm_hop)
+ *   (graph preparation and multi-GPU entry points are added below as they are built)
+ *
+ * Conventions
+ *   - plain C types only; every pointer named *_d / documented "device" is a CUDA device
+ *     pointer owned by the caller (PyTorch allocates, the library never does, except the small
+ *     opaque host-side plan struct);
+ *   - every call is stream-ordered on the cudaStream_t passed as `stream` (void* so that no CUDA
+ *     header is needed to bind it) and does not synchronise unless its comment says so;
+ *   - return value: 0 on success, a negative SGC_ERR_* code otherwise; a human-readable message
+ *     for the calling thread's last failure is available from sgc_last_error();
+ *   - index widths: row pointers are int64 (papers100M-shaped graphs exceed 2^31 bytes of
+ *     offsets), column indices are int32 (N < 2^31);
+ *   - there is no CPU fallback anywhere in this library.
+ */
+#ifndef SGC_B200_H
+#define SGC_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SGC_OK                0
+#define SGC_ERR_INVALID      -1   /* bad argument (null pointer, negative size, misaligned buffer)  */
+#define SGC_ERR_CUDA         -2   /* a CUDA runtime call failed; see sgc_last_error()               */
+#define SGC_ERR_ARCH         -3   /* device is not compute capability 10.x                          */
+#define SGC_ERR_WORKSPACE    -4   /* workspace smaller than the matching *_workspace_bytes() query  */
+#define SGC_ERR_UNSUPPORTED  -5   /* flag combination not built                                      */
+
+/* ---- housekeeping ------------------------------------------------------------------------ */
+const char *sgc_version(void);
+const char *sgc_last_error(void);
+/* Fails with SGC_ERR_ARCH unless `device` is a compute-capability-10.x GPU (B200). */
+int32_t sgc_device_check(int32_t device);
+/* Number of kernels this library has launched in the calling process (bench.py gpu_launches). */
+int64_t sgc_launch_count(void);
+
+/* ---- generic device primitives ------------------------------------------------------------ */
+size_t  sgc_scan_workspace_bytes(int64_t n);
+/* In-place exclusive prefix sum of data_d[0..n) (int64). */
+int32_t sgc_scan_exclusive_i64(int64_t *data_d, int64_t n, void *ws_d, size_t ws_bytes, void *stream);
+
+/* ---- K1: A -> canonical CSR of A + I            (normalization.py:6-7) -------------------- */
+/* flag_d[0] <- 1 if every row has strictly ascending columns in [0, n_cols), else 0.            */
+int32_t sgc_csr_check_canonical(int64_t n_rows, int64_t n_cols, const int64_t *row_ptr_d,
+                                const int32_t *col_d, int32_t *flag_d, void *stream);
+/* Sort columns inside each row and sum duplicate entries in stored order (scipy
+ * sum_duplicates).  Rows are sorted by a stable per-row rank sort.
+ * Outputs: row_ptr_out_d[n_rows+1], col_out_d / val_out_d sized nnz (upper bound); the new nnz is
+ * row_ptr_out_d[n_rows]. */
+size_t  sgc_csr_canonicalize_workspace_bytes(int64_t n_rows, int64_t nnz);
+int32_t sgc_csr_canonicalize(int64_t n_rows, int64_t nnz, const int64_t *row_ptr_d,
+                             const int32_t *col_d, const double *val_d, int64_t *row_ptr_out_d,
+                             int32_t *col_out_d, double *val_out_d, void *ws_d, size_t ws_bytes,
+                             void *stream);
+/* Pass 1: per-row entry count of A+I (existing diagonal merged, results that are exactly zero
+ * dropped, as scipy's csr_plus_csr does), exclusive-scanned into row_ptr_out_d[n+1]. Input must
+ * be canonical. */
+int32_t sgc_csr_selfloop_count(int64_t n, const int64_t *row_ptr_d, const int32_t *col_d,
+                               const double *val_d, int64_t *row_ptr_out_d, void *ws_d,
+                               size_t ws_bytes, void *stream);
+/* Pass 2: sorted merge-insert of (i,i); writes col_out_d / aval_out_d (fp64 values of A+I). */
+int32_t sgc_csr_selfloop_build(int64_t n, const int64_t *row_ptr_d, const int32_t *col_d,
+                               const double *val_d, const int64_t *row_ptr_out_d,
+                               int32_t *col_out_d, double *aval_out_d, void *stream);
+
+/* ---- K2: degree reduction and D^-1/2            (normalization.py:8-10) ------------------- */
+/* rowsum_d[i] = sum of row i of A+I accumulated in stored order in fp64; dinv_d[i] =
+ * rowsum^-1/2 (correctly rounded), +inf -> 0 (normalization.py:10); NaN for negative sums.
+ * rowsum_d may be NULL. */
+int32_t sgc_degree_inv_sqrt(int64_t n, const int64_t *row_ptr_d, const double *aval_d,
+                            double *rowsum_d, double *dinv_d, void *stream);
+
+/* ---- S = D^-1/2 (A+I) D^-1/2 structure + values (normalization.py:11-12, utils.py:25) ------ */
+/* scipy's two CSR products drop entries whose product is exactly zero (rows/columns with
+ * d == 0).  count: per-row kept entries, scanned into row_ptr_out_d[n+1]; also writes the number
+ * of dropped entries to dropped_d[0] (when 0 the input structure can be reused as is). */
+int32_t sgc_norm_count(int64_t n, const int64_t *row_ptr_d, const int32_t *col_d,
+                       const double *aval_d, const double *dinv_d, int64_t *row_ptr_out_d,
+                       int64_t *dropped_d, void *ws_d, size_t ws_bytes, void *stream);
+/* build: compacts (col, aval) to the kept entries and optionally materialises the normalised
+ * values: s64_out_d = (d_i*a_ij)*d_j in fp64 (what normalization.py:12 returns) and s32_out_d =
+ * the same rounded once to fp32 (utils.py:25).  Any of col_out_d/aval_out_d/s64_out_d/s32_out_d
+ * may be NULL.  row_ptr_out_d == row_ptr_d means "structure unchanged". */
+int32_t sgc_norm_build(int64_t n, const int64_t *row_ptr_d, const int32_t *col_d,
+                       const double *aval_d, const double *dinv_d, const int64_t *row_ptr_out_d,
+                       int32_t *col_out_d, double *aval_out_d, double *s64_out_d,
+                       float *s32_out_d, void *stream);
+/* CSR row pointers -> COO row indices (int64), and int32 -> int64 columns: the [2, nnz] index
+ * tensor of utils.py:26-27.  idx_out_d has 2*nnz int64 (rows then cols). */
+int32_t sgc_csr_to_coo(int64_t n, const int64_t *row_ptr_d, const int32_t *col_d, int64_t nnz,
+                       int64_t *idx_out_d, void *stream);
+/* Sorted COO row indices (int64) -> CSR row pointers; col int64 -> int32.  sorted_flag_d[0] is
+ * set to 0 if the input is not in row-major strictly ascending order. */
+int32_t sgc_coo_to_csr(int64_t n_rows, int64_t nnz, const int64_t *row_idx_d,
+                       const int64_t *col_idx_d, int64_t *row_ptr_out_d, int32_t *col_out_d,
+                       int32_t *sorted_flag_d, void *stream);
+
+/* ---- K3: column mean / unbiased std             (utils.py:119) ----------------------------- */
+size_t  sgc_col_stats_workspace_bytes(int64_t n, int64_t f);
+/* x_d: fp32 [n, ld] row-major.  Outputs (device, f entries each; any may be NULL):
+ * mean32/std32 (what the fused first hop consumes), mean64/std64. */
+int32_t sgc_col_stats(const float *x_d, int64_t n, int64_t f, int64_t ld, float *mean32_d,
+                      float *std32_d, double *mean64_d, double *std64_d, void *ws_d,
+                      size_t ws_bytes, void *stream);
+
+/* ---- K4: load-balanced CSR SpMM hop             (utils.py:95, torch.spmm) ------------------ */
+typedef struct sgc_plan sgc_plan_t;
+
+/* Rows longer than `chunk` stored entries are split into chunks of `chunk` entries whose partial
+ * sums are combined in chunk order by a second kernel (deterministic, no float atomics).
+ * chunk <= 0: never split -- every output element is accumulated by sequential ascending-column
+ * fp32 FMA, bit-identical to torch.spmm on CPU.  `slab_floats`: feature-slab width; all rows are
+ * processed for slab 0, then slab 1, ... so that one slab of the gathered operand stays resident
+ * in L2 (0 = library default for the shape). */
+size_t  sgc_spmm_plan_workspace_bytes(int64_t n_rows, int64_t nnz, int32_t chunk);
+/* Builds the split table on `stream`; SYNCHRONISES the stream once to read back the item count.
+ * The plan keeps pointers into ws_d and to row_ptr_d/col_d: they must outlive the plan. */
+int32_t sgc_spmm_plan_create(int64_t n_rows, int64_t n_cols, int64_t nnz,
+                             const int64_t *row_ptr_d, const int32_t *col_d, int32_t chunk,
+                             void *ws_d, size_t ws_bytes, sgc_plan_t **plan_out, void *stream);
+void    sgc_spmm_plan_destroy(sgc_plan_t *plan);
+/* Number of long-row chunk items (rows of the partial-sum buffer a hop needs). */
+int64_t sgc_spmm_plan_partial_rows(const sgc_plan_t *plan);
+
+#define SGC_HOP_FUSED_NORM   1u   /* weights = fp32((d_i*a_ij)*d_j) on the fly from aval_d + dinv_d */
+#define SGC_HOP_STD_DIV      2u   /* gathered x -> (x - mean[f]) / std[f]   (exact, utils.py:119)   */
+#define SGC_HOP_STD_RCP      4u   /* gathered x -> (x - mean[f]) * (1/std[f])  (<= 1 ulp from DIV)   */
+
+typedef struct sgc_hop_args {
+    const double *aval_d;      /* FUSED_NORM: fp64 values of A+I (pruned structure)          */
+    const double *dinv_d;      /* FUSED_NORM: D^-1/2, n_cols entries                          */
+    const float  *sval_d;      /* !FUSED_NORM: fp32 values of S                               */
+    const float  *x_d;         /* gathered operand [n_cols, ldx] fp32                         */
+    int64_t       ldx;
+    float        *y_d;         /* output [n_rows, ldy] fp32                                   */
+    int64_t       ldy;
+    float        *partial_d;   /* [sgc_spmm_plan_partial_rows(plan), ldp] scratch (may be NULL if 0 rows) */
+    int64_t       ldp;
+    const float  *mean_d;      /* STD_*: f entries                                            */
+    const float  *std_d;       /* STD_*: f entries                                            */
+    int32_t       f;           /* feature columns                                             */
+    int32_t       slab_floats; /* 0 = default                                                 */
+    uint32_t      flags;
+    int32_t       hints;       /* bit0: L2 evict_last policy on gathered x rows; bit1: evict_first on
+                                  the streamed col/value reads and the y stores                  */
+} sgc_hop_args_t;
+
+/* One hop Y = S X on `stream`. */
+int32_t sgc_spmm_hop(const sgc_plan_t *plan, const sgc_hop_args_t *args, void *stream);
+
+/* K hops (utils.py:94-95).  Hop k reads the output of hop k-1; intermediates ping-pong between
+ * buf_a_d and buf_b_d ([n, ld_buf] each; needed only when k_hops > 1 / > 2); the last hop writes
+ * args->y_d.  The standardisation flags apply to the first hop only.  Square matrices only. */
+int32_t sgc_precompute(const sgc_plan_t *plan, const sgc_hop_args_t *args, int32_t k_hops,
+                       float *buf_a_d, float *buf_b_d, int64_t ld_buf, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SGC_B200_H */

@@ -1,0 +1,10 @@
+"""sgc_b200 -- B200-native (sm_100a) implementation of SGC's feature-propagation hot path:
+``normalization.aug_normalized_adjacency`` and ``utils.sgc_precompute`` of bellaj09/SGC, behind the
+reference's own Python API.  CUDA kernels live in sgc_b200/csrc (C ABI: include/sgc_b200.h);
+PyTorch is used for device memory, streams and torch.distributed only."""
+from .graph import SgcGraph, from_scipy, from_torch_sparse, normalize_csr  # noqa: F401
+from .features import StandardizedFeatures, col_stats  # noqa: F401
+from .propagate import hop, propagate, sgc_precompute  # noqa: F401
+from .normalization import aug_normalized_adjacency, fetch_normalization, row_normalize  # noqa: F401
+
+__version__ = "0.1.0"

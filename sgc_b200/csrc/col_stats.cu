@@ -1,0 +1,113 @@
+// K3: column mean and unbiased standard deviation of a row-major fp32 matrix.
+//
+// Restates the statistics of /root/reference/utils.py:119
+//     features = (features - features.mean(dim=0)) / features.std(dim=0)
+// (torch's std is the unbiased one, divisor n-1).  One pass over X: every thread owns one column
+// of a 256-column tile and walks a contiguous block of rows, so a warp reads 128 contiguous bytes
+// per row; sums are kept in fp64 and shifted by the column's first value so that
+// sum((x-k)^2) - sum(x-k)^2/n does not cancel when |mean| >> std.  Block partials are reduced in
+// block order by a second kernel (deterministic; no atomics).  HBM-bound: reads 4*n*f bytes once.
+#include "common.cuh"
+
+namespace sgc {
+
+constexpr int CS_THREADS = 256;
+
+__global__ void __launch_bounds__(CS_THREADS)
+col_stats_partial_kernel(const float *__restrict__ x, int64_t n, int64_t f, int64_t ld,
+                         int64_t rows_per_block, double *__restrict__ part)
+{
+    const int64_t c = (int64_t)blockIdx.y * CS_THREADS + threadIdx.x;
+    const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
+    const int64_t r1 = (r0 + rows_per_block < n) ? r0 + rows_per_block : n;
+    double s1 = 0.0, s2 = 0.0;
+    if (c < f) {
+        const double k = (double)x[c];             // shift: first row of the column
+        const float *px = x + c;
+        int64_t r = r0;
+        for (; r + 4 <= r1; r += 4) {
+            const float a0 = __ldcs(px + (r + 0) * ld), a1 = __ldcs(px + (r + 1) * ld);
+            const float a2 = __ldcs(px + (r + 2) * ld), a3 = __ldcs(px + (r + 3) * ld);
+            const double d0 = (double)a0 - k, d1 = (double)a1 - k, d2 = (double)a2 - k, d3 = (double)a3 - k;
+            s1 += d0; s2 = fma(d0, d0, s2);
+            s1 += d1; s2 = fma(d1, d1, s2);
+            s1 += d2; s2 = fma(d2, d2, s2);
+            s1 += d3; s2 = fma(d3, d3, s2);
+        }
+        for (; r < r1; ++r) {
+            const double d = (double)__ldcs(px + r * ld) - k;
+            s1 += d; s2 = fma(d, d, s2);
+        }
+        part[((int64_t)blockIdx.x * 2 + 0) * f + c] = s1;
+        part[((int64_t)blockIdx.x * 2 + 1) * f + c] = s2;
+    }
+}
+
+__global__ void __launch_bounds__(CS_THREADS)
+col_stats_final_kernel(const float *__restrict__ x, int64_t n, int64_t f, int n_parts,
+                       const double *__restrict__ part, float *__restrict__ mean32,
+                       float *__restrict__ std32, double *__restrict__ mean64,
+                       double *__restrict__ std64)
+{
+    const int64_t c = (int64_t)blockIdx.x * CS_THREADS + threadIdx.x;
+    if (c >= f) return;
+    double s1 = 0.0, s2 = 0.0;
+    for (int b = 0; b < n_parts; ++b) {
+        s1 += part[((int64_t)b * 2 + 0) * f + c];
+        s2 += part[((int64_t)b * 2 + 1) * f + c];
+    }
+    const double k = (double)x[c];
+    const double dn = (double)n;
+    const double mean = k + s1 / dn;
+    double var = (s2 - s1 * s1 / dn) / (dn - 1.0);      // n == 1 -> 0/0 = NaN, like torch
+    if (var < 0.0) var = 0.0;
+    const double sd = sqrt(var);
+    if (mean32) mean32[c] = (float)mean;
+    if (std32) std32[c] = (float)sd;
+    if (mean64) mean64[c] = mean;
+    if (std64) std64[c] = sd;
+}
+
+static int stats_blocks(int64_t n)
+{
+    int64_t b = ceil_div(n, 64);                 // at least 64 rows per block
+    const int64_t cap = (int64_t)sm_count() * 4;
+    if (b > cap) b = cap;
+    if (b < 1) b = 1;
+    return (int)b;
+}
+
+}  // namespace sgc
+
+using namespace sgc;
+
+extern "C" {
+
+size_t sgc_col_stats_workspace_bytes(int64_t n, int64_t f)
+{
+    return (size_t)stats_blocks(n) * 2 * (size_t)(f > 0 ? f : 1) * sizeof(double) + 256;
+}
+
+int32_t sgc_col_stats(const float *x_d, int64_t n, int64_t f, int64_t ld, float *mean32_d,
+                      float *std32_d, double *mean64_d, double *std64_d, void *ws_d,
+                      size_t ws_bytes, void *stream)
+{
+    SGC_REQUIRE(x_d && n >= 1 && f >= 1 && ld >= f, "col_stats: bad arguments (n=%lld f=%lld ld=%lld)",
+                (long long)n, (long long)f, (long long)ld);
+    if (!ws_d || ws_bytes < sgc_col_stats_workspace_bytes(n, f)) {
+        set_error("col_stats: workspace too small");
+        return SGC_ERR_WORKSPACE;
+    }
+    cudaStream_t s = as_stream(stream);
+    const int nb = stats_blocks(n);
+    const int64_t rows_per_block = ceil_div(n, nb);
+    const unsigned tiles = (unsigned)ceil_div(f, CS_THREADS);
+    double *part = reinterpret_cast<double *>(ws_d);
+    col_stats_partial_kernel<<<dim3((unsigned)nb, tiles), CS_THREADS, 0, s>>>(x_d, n, f, ld, rows_per_block, part);
+    SGC_LAUNCH_CHECK();
+    col_stats_final_kernel<<<tiles, CS_THREADS, 0, s>>>(x_d, n, f, nb, part, mean32_d, std32_d, mean64_d, std64_d);
+    SGC_LAUNCH_CHECK();
+    return SGC_OK;
+}
+
+}  // extern "C"

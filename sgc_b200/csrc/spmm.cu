@@ -1,0 +1,319 @@
+// K4 host side: split-table ("plan") construction, kernel selection, the hop and K-hop entry
+// points.  Kernels are in spmm.cuh; see there for the work decomposition.
+#include <new>
+
+#include "spmm.cuh"
+
+namespace sgc {
+
+hop_launch_fn find_hop_kernel_v4(int g, int u, bool fused, int stdmode);
+hop_launch_fn find_hop_kernel_v2(int g, int u, bool fused, int stdmode);
+hop_launch_fn find_hop_kernel_v1(int g, int u, bool fused, int stdmode);
+
+hop_launch_fn find_hop_kernel(int g, int vec, int u, bool fused, int stdmode)
+{
+    if (vec == 4) return find_hop_kernel_v4(g, u, fused, stdmode);
+    if (vec == 2) return find_hop_kernel_v2(g, u, fused, stdmode);
+    if (vec == 1) return find_hop_kernel_v1(g, u, fused, stdmode);
+    return nullptr;
+}
+
+// ---- plan construction ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+plan_count_kernel(int64_t n, const int64_t *__restrict__ row_ptr, int32_t chunk,
+                  int64_t *__restrict__ n_chunks, int64_t *__restrict__ is_long)
+{
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i <= n;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        int64_t c = 0;
+        if (i < n) {
+            const int64_t len = row_ptr[i + 1] - row_ptr[i];
+            if (len > chunk) c = (len + chunk - 1) / chunk;
+        }
+        n_chunks[i] = c;
+        is_long[i] = c > 0 ? 1 : 0;
+    }
+}
+
+__global__ void __launch_bounds__(256)
+plan_fill_kernel(int64_t n, const int64_t *__restrict__ row_ptr, int32_t chunk,
+                 const int64_t *__restrict__ chunk_off, const int64_t *__restrict__ long_off,
+                 int32_t *__restrict__ li_row, int64_t *__restrict__ li_beg,
+                 int32_t *__restrict__ li_len, int32_t *__restrict__ lr_row,
+                 int64_t *__restrict__ lr_first, int32_t *__restrict__ lr_cnt)
+{
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t b = row_ptr[i], e = row_ptr[i + 1];
+        if (e - b <= chunk) continue;
+        const int64_t first = chunk_off[i];
+        const int64_t cnt = chunk_off[i + 1] - first;
+        const int64_t k = long_off[i];
+        lr_row[k] = (int32_t)i;
+        lr_first[k] = first;
+        lr_cnt[k] = (int32_t)cnt;
+        for (int64_t c = 0; c < cnt; ++c) {
+            const int64_t cb = b + c * chunk;
+            li_row[first + c] = (int32_t)i;
+            li_beg[first + c] = cb;
+            li_len[first + c] = (int32_t)((e - cb < chunk) ? (e - cb) : chunk);
+        }
+    }
+}
+
+// y[row] = partial[first] + partial[first+1] + ... in chunk order; one thread per
+// (long row, feature), consecutive threads on consecutive features.
+__global__ void __launch_bounds__(256)
+spmm_fixup_kernel(int64_t n_long_rows, const int32_t *__restrict__ lr_row,
+                  const int64_t *__restrict__ lr_first, const int32_t *__restrict__ lr_cnt,
+                  const float *__restrict__ partial, int64_t ldp, float *__restrict__ y,
+                  int64_t ldy, int32_t f)
+{
+    const int64_t k = blockIdx.x;
+    if (k >= n_long_rows) return;
+    const int64_t row = lr_row[k], first = lr_first[k];
+    const int cnt = lr_cnt[k];
+    for (int c = threadIdx.x; c < f; c += blockDim.x) {
+        float acc = partial[first * ldp + c];
+        for (int j = 1; j < cnt; ++j) acc = __fadd_rn(acc, partial[(first + j) * ldp + c]);
+        y[row * ldy + c] = acc;
+    }
+}
+
+static inline size_t align256(size_t v) { return (v + 255) / 256 * 256; }
+
+struct PlanLayout {
+    size_t off_chunks, off_long, off_scan, scan_bytes;
+    size_t off_li_row, off_li_len, off_li_beg, off_lr_row, off_lr_cnt, off_lr_first, total;
+    int64_t max_items, max_long;
+};
+
+static PlanLayout plan_layout(int64_t n_rows, int64_t nnz, int32_t chunk)
+{
+    PlanLayout L{};
+    if (chunk <= 0) { L.total = 256; return L; }
+    L.max_long = nnz / chunk + 1;
+    L.max_items = 2 * (nnz / chunk) + 2;
+    size_t o = 0;
+    L.off_chunks = o; o += align256((size_t)(n_rows + 1) * 8);
+    L.off_long = o;   o += align256((size_t)(n_rows + 1) * 8);
+    L.scan_bytes = scan_workspace_bytes(n_rows + 1);
+    L.off_scan = o;   o += align256(L.scan_bytes);
+    L.off_li_row = o; o += align256((size_t)L.max_items * 4);
+    L.off_li_len = o; o += align256((size_t)L.max_items * 4);
+    L.off_li_beg = o; o += align256((size_t)L.max_items * 8);
+    L.off_lr_row = o; o += align256((size_t)L.max_long * 4);
+    L.off_lr_cnt = o; o += align256((size_t)L.max_long * 4);
+    L.off_lr_first = o; o += align256((size_t)L.max_long * 8);
+    L.total = o + 256;
+    return L;
+}
+
+// Default slab width (floats) for a gathered operand of n_cols rows: the widest slab whose
+// N x SW x 4-byte working set fits the L2 budget; whole rows when everything fits.
+static int default_slab(int64_t n_cols, int f, int vec)
+{
+    const double budget = 56.0 * 1024 * 1024;      // ~ half of the 126 MB L2 (two-die replication)
+    const int widths4[] = {256, 128, 64, 32};
+    const int widths2[] = {128, 64, 32};
+    const int widths1[] = {64, 32};
+    const int *w = vec == 4 ? widths4 : (vec == 2 ? widths2 : widths1);
+    const int nw = vec == 4 ? 4 : (vec == 2 ? 3 : 2);
+    int best = w[nw - 1];
+    for (int i = nw - 1; i >= 0; --i) {
+        if ((double)n_cols * w[i] * 4.0 <= budget) best = w[i];
+    }
+    // never wider than needed to cover f in one slab
+    for (int i = nw - 1; i >= 0; --i)
+        if (w[i] >= f && w[i] < best) best = w[i];
+    return best;
+}
+
+static bool slab_shape(int slab, int vec, int *g, int *u)
+{
+    const int lanes = slab / vec;     // G * U
+    if (lanes == 64) { *g = 32; *u = 2; return true; }
+    if (lanes == 32 || lanes == 16 || lanes == 8) { *g = lanes; *u = 1; return true; }
+    return false;
+}
+
+static int32_t run_hop(const sgc_plan_impl *pl, const sgc_hop_args_t *a, const float *x,
+                       int64_t ldx, float *y, int64_t ldy, uint32_t flags, cudaStream_t s)
+{
+    const bool fused = (flags & SGC_HOP_FUSED_NORM) != 0;
+    const int stdmode = (flags & SGC_HOP_STD_DIV) ? 1 : ((flags & SGC_HOP_STD_RCP) ? 2 : 0);
+    SGC_REQUIRE(x && y && a->f >= 1 && ldx >= a->f && ldy >= a->f, "spmm_hop: bad operand shape");
+    SGC_REQUIRE(x != y, "spmm_hop: in-place hop is not supported");
+    if (fused) SGC_REQUIRE(a->aval_d && a->dinv_d, "spmm_hop: FUSED_NORM needs aval_d and dinv_d");
+    else SGC_REQUIRE(a->sval_d || pl->nnz == 0, "spmm_hop: sval_d is null");
+    if (stdmode) SGC_REQUIRE(a->mean_d && a->std_d, "spmm_hop: standardisation needs mean_d and std_d");
+    if (pl->n_long_items > 0)
+        SGC_REQUIRE(a->partial_d && a->ldp >= a->f && a->ldp % 4 == 0 &&
+                        (reinterpret_cast<uintptr_t>(a->partial_d) & 15) == 0,
+                    "spmm_hop: partial_d must be 16-byte aligned with ldp %% 4 == 0 and ldp >= f");
+    if (pl->n_rows == 0) return SGC_OK;
+
+    int vec = 1;
+    if (ldx % 4 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0) vec = 4;
+    else if (ldx % 2 == 0 && (reinterpret_cast<uintptr_t>(x) & 7) == 0) vec = 2;
+    int y_vec = 1;
+    if (ldy % 4 == 0 && (reinterpret_cast<uintptr_t>(y) & 15) == 0) y_vec = 4;
+    else if (ldy % 2 == 0 && (reinterpret_cast<uintptr_t>(y) & 7) == 0) y_vec = 2;
+
+    int slab = a->slab_floats > 0 ? a->slab_floats : default_slab(pl->n_cols, a->f, vec);
+    int g = 0, u = 0;
+    if (!slab_shape(slab, vec, &g, &u)) {
+        // requested width not built for this alignment: fall to the nearest built one
+        slab = default_slab(pl->n_cols, a->f, vec);
+        if (!slab_shape(slab, vec, &g, &u)) {
+            set_error("spmm_hop: no kernel for slab %d vec %d", slab, vec);
+            return SGC_ERR_UNSUPPORTED;
+        }
+    }
+    hop_launch_fn fn = find_hop_kernel(g, vec, u, fused, stdmode);
+    if (!fn) {
+        set_error("spmm_hop: kernel variant g=%d vec=%d u=%d fused=%d std=%d not built", g, vec, u,
+                  (int)fused, stdmode);
+        return SGC_ERR_UNSUPPORTED;
+    }
+
+    HopDev p{};
+    p.row_ptr = pl->row_ptr; p.col = pl->col;
+    p.aval = a->aval_d; p.dinv = a->dinv_d; p.sval = a->sval_d;
+    p.x = x; p.ldx = ldx; p.y = y; p.ldy = ldy;
+    p.partial = a->partial_d; p.ldp = a->ldp;
+    p.mean = a->mean_d; p.stdv = a->std_d;
+    p.li_row = pl->li_row; p.li_beg = pl->li_beg; p.li_len = pl->li_len;
+    p.n_rows = pl->n_rows; p.n_long_items = pl->n_long_items;
+    p.f = a->f; p.chunk = pl->chunk;
+    p.n_slabs = (a->f + slab - 1) / slab;
+    p.y_vec = y_vec;
+    p.hints = a->hints & 3;
+    const int64_t n_tasks = (int64_t)p.n_slabs * (p.n_long_items + p.n_rows);
+    int32_t rc = fn(p, n_tasks, s);
+    if (rc != SGC_OK) return rc;
+    if (pl->n_long_rows > 0) {
+        spmm_fixup_kernel<<<(unsigned)pl->n_long_rows, 256, 0, s>>>(
+            pl->n_long_rows, pl->lr_row, pl->lr_first, pl->lr_cnt, a->partial_d, a->ldp, y, ldy, a->f);
+        SGC_LAUNCH_CHECK();
+    }
+    return SGC_OK;
+}
+
+}  // namespace sgc
+
+using namespace sgc;
+
+struct sgc_plan { sgc_plan_impl impl; };
+
+extern "C" {
+
+size_t sgc_spmm_plan_workspace_bytes(int64_t n_rows, int64_t nnz, int32_t chunk)
+{
+    if (n_rows < 0 || nnz < 0) return 0;
+    return plan_layout(n_rows, nnz, chunk).total;
+}
+
+int32_t sgc_spmm_plan_create(int64_t n_rows, int64_t n_cols, int64_t nnz,
+                             const int64_t *row_ptr_d, const int32_t *col_d, int32_t chunk,
+                             void *ws_d, size_t ws_bytes, sgc_plan_t **plan_out, void *stream)
+{
+    SGC_REQUIRE(plan_out, "spmm_plan_create: plan_out is null");
+    *plan_out = nullptr;
+    SGC_REQUIRE(n_rows >= 0 && n_cols >= 0 && nnz >= 0 && row_ptr_d, "spmm_plan_create: bad arguments");
+    SGC_REQUIRE(n_rows < 0x7fffffffLL && n_cols < 0x7fffffffLL, "spmm_plan_create: more than 2^31-1 rows/cols");
+    SGC_REQUIRE(nnz == 0 || col_d, "spmm_plan_create: col_d is null");
+    if (chunk < 0) chunk = 0;
+    if (chunk > 0 && chunk < 32) chunk = 32;
+    const PlanLayout L = plan_layout(n_rows, nnz, chunk);
+    if (chunk > 0 && (!ws_d || ws_bytes < L.total)) {
+        set_error("spmm_plan_create: workspace too small (%zu < %zu)", ws_bytes, L.total);
+        return SGC_ERR_WORKSPACE;
+    }
+    cudaStream_t s = as_stream(stream);
+    sgc_plan *pl = new (std::nothrow) sgc_plan();
+    SGC_REQUIRE(pl, "spmm_plan_create: out of host memory");
+    sgc_plan_impl &P = pl->impl;
+    P.n_rows = n_rows; P.n_cols = n_cols; P.nnz = nnz;
+    P.row_ptr = row_ptr_d; P.col = col_d; P.chunk = chunk;
+    if (chunk > 0 && n_rows > 0) {
+        char *ws = reinterpret_cast<char *>(ws_d);
+        int64_t *n_chunks = reinterpret_cast<int64_t *>(ws + L.off_chunks);
+        int64_t *is_long = reinterpret_cast<int64_t *>(ws + L.off_long);
+        const int grid = grid_for(ceil_div(n_rows + 1, 256), 8);
+        plan_count_kernel<<<grid, 256, 0, s>>>(n_rows, row_ptr_d, chunk, n_chunks, is_long);
+        count_launch();
+        int32_t rc = scan_exclusive_i64(n_chunks, n_rows + 1, ws + L.off_scan, L.scan_bytes, s);
+        if (rc == SGC_OK) rc = scan_exclusive_i64(is_long, n_rows + 1, ws + L.off_scan, L.scan_bytes, s);
+        int64_t totals[2] = {0, 0};
+        cudaError_t e = cudaSuccess;
+        if (rc == SGC_OK) {
+            e = cudaMemcpyAsync(&totals[0], n_chunks + n_rows, 8, cudaMemcpyDeviceToHost, s);
+            if (e == cudaSuccess) e = cudaMemcpyAsync(&totals[1], is_long + n_rows, 8, cudaMemcpyDeviceToHost, s);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+            if (e != cudaSuccess) rc = cuda_fail(e, "plan readback", __FILE__, __LINE__);
+        }
+        if (rc == SGC_OK && (totals[0] > L.max_items || totals[1] > L.max_long)) {
+            set_error("spmm_plan_create: internal bound exceeded");
+            rc = SGC_ERR_INVALID;
+        }
+        if (rc != SGC_OK) { delete pl; return rc; }
+        P.n_long_items = totals[0];
+        P.n_long_rows = totals[1];
+        int32_t *li_row = reinterpret_cast<int32_t *>(ws + L.off_li_row);
+        int32_t *li_len = reinterpret_cast<int32_t *>(ws + L.off_li_len);
+        int64_t *li_beg = reinterpret_cast<int64_t *>(ws + L.off_li_beg);
+        int32_t *lr_row = reinterpret_cast<int32_t *>(ws + L.off_lr_row);
+        int32_t *lr_cnt = reinterpret_cast<int32_t *>(ws + L.off_lr_cnt);
+        int64_t *lr_first = reinterpret_cast<int64_t *>(ws + L.off_lr_first);
+        if (P.n_long_rows > 0) {
+            plan_fill_kernel<<<grid, 256, 0, s>>>(n_rows, row_ptr_d, chunk, n_chunks, is_long, li_row,
+                                                 li_beg, li_len, lr_row, lr_first, lr_cnt);
+            count_launch();
+        }
+        P.li_row = li_row; P.li_len = li_len; P.li_beg = li_beg;
+        P.lr_row = lr_row; P.lr_cnt = lr_cnt; P.lr_first = lr_first;
+        e = cudaPeekAtLastError();
+        if (e != cudaSuccess) { delete pl; return cuda_fail(e, "plan kernels", __FILE__, __LINE__); }
+    }
+    *plan_out = pl;
+    return SGC_OK;
+}
+
+void sgc_spmm_plan_destroy(sgc_plan_t *plan) { delete plan; }
+
+int64_t sgc_spmm_plan_partial_rows(const sgc_plan_t *plan) { return plan ? plan->impl.n_long_items : 0; }
+
+int32_t sgc_spmm_hop(const sgc_plan_t *plan, const sgc_hop_args_t *args, void *stream)
+{
+    SGC_REQUIRE(plan && args, "spmm_hop: null plan or args");
+    return run_hop(&plan->impl, args, args->x_d, args->ldx, args->y_d, args->ldy, args->flags,
+                   as_stream(stream));
+}
+
+int32_t sgc_precompute(const sgc_plan_t *plan, const sgc_hop_args_t *args, int32_t k_hops,
+                       float *buf_a_d, float *buf_b_d, int64_t ld_buf, void *stream)
+{
+    SGC_REQUIRE(plan && args, "precompute: null plan or args");
+    SGC_REQUIRE(k_hops >= 1, "precompute: k_hops must be >= 1 (degree 0 returns the input on the host side)");
+    SGC_REQUIRE(plan->impl.n_rows == plan->impl.n_cols, "precompute: K-hop propagation needs a square matrix");
+    if (k_hops >= 2) SGC_REQUIRE(buf_a_d && ld_buf >= args->f, "precompute: buf_a_d required for k_hops >= 2");
+    if (k_hops >= 3) SGC_REQUIRE(buf_b_d, "precompute: buf_b_d required for k_hops >= 3");
+    cudaStream_t s = as_stream(stream);
+    const uint32_t std_bits = SGC_HOP_STD_DIV | SGC_HOP_STD_RCP;
+    const float *src = args->x_d;
+    int64_t ld_src = args->ldx;
+    for (int k = 0; k < k_hops; ++k) {
+        const bool last = (k == k_hops - 1);
+        float *dst = last ? args->y_d : ((k & 1) ? buf_b_d : buf_a_d);
+        const int64_t ld_dst = last ? args->ldy : ld_buf;
+        const uint32_t flags = (k == 0) ? args->flags : (args->flags & ~std_bits);
+        int32_t rc = run_hop(&plan->impl, args, src, ld_src, dst, ld_dst, flags, s);
+        if (rc != SGC_OK) return rc;
+        src = dst;
+        ld_src = ld_dst;
+    }
+    return SGC_OK;
+}
+
+}  // extern "C"

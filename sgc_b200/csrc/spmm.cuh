@@ -1,0 +1,330 @@
+// K4: the propagation hop  Y = S X  (what torch.spmm does at /root/reference/utils.py:95) as a
+// load-balanced CSR SpMM for sm_100a.
+//
+// Work decomposition
+//   task  = (feature slab, row-or-chunk).  Tasks are numbered slab-major, so the grid sweeps all
+//           rows for feature columns [0, SW), then [SW, 2SW), ...: the gathered operand touched
+//           at any time is N x SW floats, which the caller sizes to stay resident in the 126 MB
+//           L2 (two dies: ~half of it is usable for data every SM reads) while col/val stream
+//           through with an evict-first policy.
+//   group = G lanes own one task; a warp runs 32/G tasks.  Each lane keeps U vectors of VEC
+//           floats of the output row in registers (slab width SW = G*VEC*U).
+//   rows longer than `chunk` entries are split at plan time into chunk items whose partial sums
+//           go to a scratch matrix and are combined in chunk order by spmm_fixup_kernel
+//           (deterministic; no float atomics).  Unsplit rows are accumulated by sequential
+//           ascending-column fp32 FMA, the order torch.spmm uses on the CPU.
+//
+// Inner loop: the G lanes of a group load G (col, value) pairs with one coalesced access, turn
+// them into fp32 weights (fused mode: fp32((d_i*a_ij)*d_j) from the fp64 A+I value and D^-1/2,
+// so S is never materialised), then broadcast them lane by lane with shuffles while every lane
+// issues UNR independent 16-byte gathers of its piece of the neighbour rows before the FMAs that
+// consume them.  Optional first-hop standardisation (x-mean)/std is applied to the gathered
+// value in registers.
+#pragma once
+#include "common.cuh"
+
+namespace sgc {
+
+constexpr int HOP_THREADS = 128;
+
+struct HopDev {
+    const int64_t *row_ptr;
+    const int32_t *col;
+    const double *aval;
+    const double *dinv;
+    const float *sval;
+    const float *x;
+    int64_t ldx;
+    float *y;
+    int64_t ldy;
+    float *partial;
+    int64_t ldp;
+    const float *mean;
+    const float *stdv;
+    const int32_t *li_row;
+    const int64_t *li_beg;
+    const int32_t *li_len;
+    int64_t n_rows;
+    int64_t n_long_items;
+    int32_t f;
+    int32_t chunk;
+    int32_t n_slabs;
+    int32_t y_vec;       // widest legal vector store into y (1, 2 or 4 floats)
+    int32_t hints;       // bit0: L2 evict_last on gathered rows; bit1: evict_first on streams
+};
+
+struct sgc_plan_impl {
+    int64_t n_rows, n_cols, nnz;
+    const int64_t *row_ptr;
+    const int32_t *col;
+    int32_t chunk;
+    int64_t n_long_items, n_long_rows;
+    const int32_t *li_row;
+    const int64_t *li_beg;
+    const int32_t *li_len;
+    const int32_t *lr_row;
+    const int64_t *lr_first;
+    const int32_t *lr_cnt;
+};
+
+typedef int32_t (*hop_launch_fn)(const HopDev &, int64_t n_tasks, cudaStream_t);
+
+// Filled by the instantiation units (spmm_inst_*.cu).
+hop_launch_fn find_hop_kernel(int g, int vec, int u, bool fused, int stdmode);
+
+#ifdef __CUDACC__
+
+__device__ __forceinline__ uint64_t l2_policy(int kind)
+{
+    uint64_t p;
+    if (kind == 1)
+        asm("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+    else if (kind == 2)
+        asm("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+    else
+        asm("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+
+template <int VEC> struct Vec;
+template <> struct Vec<4> {
+    float v[4];
+    __device__ __forceinline__ void load(const float *p, uint64_t pol)
+    {
+        asm volatile("ld.global.nc.L2::cache_hint.v4.f32 {%0,%1,%2,%3}, [%4], %5;"
+                     : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]) : "l"(p), "l"(pol));
+    }
+    // Zero-instruction scheduling fence: volatile asm statements keep their program order, so
+    // every gather of a batch is issued before the first FMA that consumes one.
+    __device__ __forceinline__ void pin() { asm volatile("" : "+f"(v[0]), "+f"(v[1]), "+f"(v[2]), "+f"(v[3])); }
+};
+template <> struct Vec<2> {
+    float v[2];
+    __device__ __forceinline__ void load(const float *p, uint64_t pol)
+    {
+        asm volatile("ld.global.nc.L2::cache_hint.v2.f32 {%0,%1}, [%2], %3;"
+                     : "=f"(v[0]), "=f"(v[1]) : "l"(p), "l"(pol));
+    }
+    __device__ __forceinline__ void pin() { asm volatile("" : "+f"(v[0]), "+f"(v[1])); }
+};
+template <> struct Vec<1> {
+    float v[1];
+    __device__ __forceinline__ void load(const float *p, uint64_t pol)
+    {
+        asm volatile("ld.global.nc.L2::cache_hint.f32 %0, [%1], %2;" : "=f"(v[0]) : "l"(p), "l"(pol));
+    }
+    __device__ __forceinline__ void pin() { asm volatile("" : "+f"(v[0])); }
+};
+
+__device__ __forceinline__ int32_t ld_stream_i32(const int32_t *p, uint64_t pol)
+{
+    int32_t r;
+    asm("ld.global.nc.L1::no_allocate.L2::cache_hint.s32 %0, [%1], %2;" : "=r"(r) : "l"(p), "l"(pol));
+    return r;
+}
+__device__ __forceinline__ float ld_stream_f32(const float *p, uint64_t pol)
+{
+    float r;
+    asm("ld.global.nc.L1::no_allocate.L2::cache_hint.f32 %0, [%1], %2;" : "=f"(r) : "l"(p), "l"(pol));
+    return r;
+}
+__device__ __forceinline__ double ld_stream_f64(const double *p, uint64_t pol)
+{
+    double r;
+    asm("ld.global.nc.L1::no_allocate.L2::cache_hint.f64 %0, [%1], %2;" : "=d"(r) : "l"(p), "l"(pol));
+    return r;
+}
+
+__device__ __forceinline__ void st_hint_v4(float *p, const float *v, uint64_t pol)
+{
+    asm volatile("st.global.L2::cache_hint.v4.f32 [%0], {%1,%2,%3,%4}, %5;"
+                 :: "l"(p), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]), "l"(pol) : "memory");
+}
+__device__ __forceinline__ void st_hint_v2(float *p, const float *v, uint64_t pol)
+{
+    asm volatile("st.global.L2::cache_hint.v2.f32 [%0], {%1,%2}, %3;"
+                 :: "l"(p), "f"(v[0]), "f"(v[1]), "l"(pol) : "memory");
+}
+__device__ __forceinline__ void st_hint_v1(float *p, float v, uint64_t pol)
+{
+    asm volatile("st.global.L2::cache_hint.f32 [%0], %1, %2;" :: "l"(p), "f"(v), "l"(pol) : "memory");
+}
+
+// STD: 0 none, 1 exact division, 2 multiply by reciprocal
+template <int STD>
+__device__ __forceinline__ float standardize(float x, float mu, float s)
+{
+    if (STD == 1) return __fdiv_rn(__fsub_rn(x, mu), s);
+    if (STD == 2) return __fmul_rn(__fsub_rn(x, mu), s);
+    return x;
+}
+
+template <int G, int VEC, int U, bool FUSED, int STD>
+__global__ void __launch_bounds__(HOP_THREADS, 5)
+spmm_hop_kernel(const HopDev p)
+{
+    constexpr int GPW = 32 / G;                       // tasks per warp
+    constexpr int SW = G * VEC * U;                   // slab width in floats
+    constexpr int UNR = (U * VEC >= 8) ? 4 : 8;       // gathers in flight per lane
+    static_assert(G % UNR == 0, "unroll must divide the group size");
+
+    const int lane = threadIdx.x & 31;
+    const int gl = lane % G;
+    const int64_t warp = (int64_t)blockIdx.x * (HOP_THREADS / 32) + (threadIdx.x >> 5);
+    const int64_t task = warp * GPW + lane / G;
+    const int64_t per_slab = p.n_long_items + p.n_rows;
+    const int64_t slab = task / per_slab;
+    const int64_t t = task - slab * per_slab;
+
+    const uint64_t pol_x = l2_policy((p.hints & 1) ? 1 : 0);
+    const uint64_t pol_s = l2_policy((p.hints & 2) ? 2 : 0);
+
+    bool valid = slab < p.n_slabs;
+    int64_t row = 0, beg = 0, end = 0;
+    float *dst = nullptr;
+    bool to_y = true;
+    if (valid) {
+        if (t < p.n_long_items) {
+            row = p.li_row[t];
+            beg = p.li_beg[t];
+            end = beg + p.li_len[t];
+            dst = p.partial + t * p.ldp;
+            to_y = false;
+        } else {
+            row = t - p.n_long_items;
+            beg = p.row_ptr[row];
+            end = p.row_ptr[row + 1];
+            if (p.chunk > 0 && end - beg > p.chunk) valid = false;   // owned by chunk items
+            dst = p.y + row * p.ldy;
+        }
+    }
+    if (!valid) beg = end = 0;
+
+    const int f0 = (int)slab * SW;
+    int fo[U], fo_ld[U];
+    bool act[U];
+    float mu[U][VEC], sg[U][VEC];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+        fo[u] = f0 + (u * G + gl) * VEC;
+        act[u] = valid && fo[u] < p.f;
+        fo_ld[u] = act[u] ? fo[u] : 0;
+#pragma unroll
+        for (int v = 0; v < VEC; ++v) {
+            mu[u][v] = 0.f;
+            sg[u][v] = 1.f;
+            if (STD != 0 && act[u] && fo[u] + v < p.f) {
+                mu[u][v] = p.mean[fo[u] + v];
+                const float s = p.stdv[fo[u] + v];
+                sg[u][v] = (STD == 2) ? __frcp_rn(s) : s;
+            }
+        }
+    }
+
+    float acc[U][VEC];
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+#pragma unroll
+        for (int v = 0; v < VEC; ++v) acc[u][v] = 0.f;
+
+    const double di = (FUSED && valid) ? p.dinv[row] : 0.0;
+    const int len = (int)(end - beg);
+    const int nb = (len + G - 1) / G;
+    const int nb_max = (GPW == 1) ? nb : __reduce_max_sync(0xffffffffu, nb);
+
+    for (int bt = 0; bt < nb_max; ++bt) {
+        const int64_t base = beg + (int64_t)bt * G;
+        const int64_t idx = base + gl;
+        int32_t c = 0;
+        float w = 0.f;
+        if (idx < end) {
+            c = ld_stream_i32(p.col + idx, pol_s);
+            if (FUSED) {
+                const double a = ld_stream_f64(p.aval + idx, pol_s);
+                const double dj = __ldg(p.dinv + c);
+                w = __double2float_rn(norm_value64(di, a, dj));
+            } else {
+                w = ld_stream_f32(p.sval + idx, pol_s);
+            }
+        }
+        int cnt = (int)(end - base);
+        cnt = cnt < 0 ? 0 : (cnt > G ? G : cnt);
+        const int cnt_max = (GPW == 1) ? cnt : __reduce_max_sync(0xffffffffu, cnt);
+
+        for (int j0 = 0; j0 < cnt_max; j0 += UNR) {
+            int32_t cj[UNR];
+            float wj[UNR];
+            Vec<VEC> xv[UNR][U];
+#pragma unroll
+            for (int jj = 0; jj < UNR; ++jj) {
+                cj[jj] = __shfl_sync(0xffffffffu, c, j0 + jj, G);
+                wj[jj] = __shfl_sync(0xffffffffu, w, j0 + jj, G);
+            }
+            // Gathers are unconditional: lanes past the end of their row hold column 0 and lanes
+            // past the last feature read offset 0, so every address is valid; only the FMAs are
+            // predicated.  This keeps the UNR loads back to back in the instruction stream.
+#pragma unroll
+            for (int jj = 0; jj < UNR; ++jj) {
+                const float *xr = p.x + (int64_t)cj[jj] * p.ldx;
+#pragma unroll
+                for (int u = 0; u < U; ++u) xv[jj][u].load(xr + fo_ld[u], pol_x);
+            }
+#pragma unroll
+            for (int jj = 0; jj < UNR; ++jj)
+#pragma unroll
+                for (int u = 0; u < U; ++u) xv[jj][u].pin();
+#pragma unroll
+            for (int jj = 0; jj < UNR; ++jj) {
+                if (j0 + jj < cnt) {
+#pragma unroll
+                    for (int u = 0; u < U; ++u)
+#pragma unroll
+                        for (int v = 0; v < VEC; ++v)
+                            acc[u][v] = __fmaf_rn(wj[jj],
+                                                  standardize<STD>(xv[jj][u].v[v], mu[u][v], sg[u][v]),
+                                                  acc[u][v]);
+                }
+            }
+        }
+    }
+
+    if (!valid) return;
+    const int sv = to_y ? (p.y_vec < VEC ? p.y_vec : VEC) : VEC;   // partial rows are padded and aligned
+    const uint64_t pol_y = pol_s;
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+        if (!act[u]) continue;
+        float *q = dst + fo[u];
+        if (VEC == 4 && sv == 4) {
+            st_hint_v4(q, acc[u], pol_y);
+        } else if (VEC >= 2 && sv >= 2) {
+#pragma unroll
+            for (int v = 0; v < VEC; v += 2)
+                if (fo[u] + v < p.f) st_hint_v2(q + v, &acc[u][v], pol_y);
+        } else {
+#pragma unroll
+            for (int v = 0; v < VEC; ++v)
+                if (fo[u] + v < p.f) st_hint_v1(q + v, acc[u][v], pol_y);
+        }
+    }
+}
+
+template <int G, int VEC, int U, bool FUSED, int STD>
+int32_t launch_hop(const HopDev &p, int64_t n_tasks, cudaStream_t s)
+{
+    constexpr int GPW = 32 / G;
+    const int64_t warps = ceil_div(n_tasks, GPW);
+    const int64_t blocks = ceil_div(warps, HOP_THREADS / 32);
+    if (blocks <= 0) return SGC_OK;
+    if (blocks > 0x7fffffffLL) {
+        set_error("spmm_hop: grid too large (%lld blocks)", (long long)blocks);
+        return SGC_ERR_INVALID;
+    }
+    spmm_hop_kernel<G, VEC, U, FUSED, STD><<<(unsigned)blocks, HOP_THREADS, 0, s>>>(p);
+    SGC_LAUNCH_CHECK();
+    return SGC_OK;
+}
+
+#endif  // __CUDACC__
+
+}  // namespace sgc

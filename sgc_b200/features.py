@@ -1,0 +1,99 @@
+"""Feature-side pieces of the path: column statistics (K3) and the lazily standardised feature
+matrix that lets the first propagation hop apply ``(x - mean) / std`` in registers.
+
+Reference behaviour being replaced: /root/reference/utils.py:118-119
+    features = torch.FloatTensor(np.array(features))
+    features = (features - features.mean(dim=0)) / features.std(dim=0)
+which materialises a standardised copy on the CPU.  Here `load_reddit_data` returns a
+`StandardizedFeatures`: the raw fp32 matrix in HBM plus fp32 mean/std vectors.  It behaves like the
+standardised tensor for every consumer (any torch op on it sees ``(raw-mean)/std``), row selection
+(``features[idx_train]``, reddit.py:45) stays lazy, and ``sgc_precompute`` hands raw + statistics
+to the fused first hop.
+"""
+import torch
+
+from . import _ffi
+from .graph import require_cuda, stream_ptr
+
+
+def col_stats(x, want64=False):
+    """Column mean and unbiased std of a CUDA fp32 [N, F] matrix, computed by sgc_col_stats with
+    fp64 accumulation.  Returns (mean32, std32) or (mean32, std32, mean64, std64)."""
+    dev = require_cuda(x.device)
+    if x.dtype != torch.float32 or x.dim() != 2:
+        raise TypeError("col_stats expects a 2-D float32 tensor")
+    if x.stride(1) != 1:
+        x = x.contiguous()
+    n, f = x.shape
+    lib = _ffi.lib()
+    with torch.cuda.device(dev):
+        mean32 = torch.empty(f, dtype=torch.float32, device=dev)
+        std32 = torch.empty(f, dtype=torch.float32, device=dev)
+        mean64 = torch.empty(f, dtype=torch.float64, device=dev) if want64 else None
+        std64 = torch.empty(f, dtype=torch.float64, device=dev) if want64 else None
+        ws = torch.empty(lib.sgc_col_stats_workspace_bytes(n, f), dtype=torch.uint8, device=dev)
+        _ffi.call("sgc_col_stats", x.data_ptr(), n, f, x.stride(0), _ffi.ptr(mean32), _ffi.ptr(std32),
+                  _ffi.ptr(mean64), _ffi.ptr(std64), _ffi.ptr(ws), ws.numel(), stream_ptr())
+    return (mean32, std32, mean64, std64) if want64 else (mean32, std32)
+
+
+def _getter(name):
+    return getattr(torch.Tensor, name).__get__
+
+
+_METADATA = {
+    torch.Tensor.size, torch.Tensor.dim, torch.Tensor.stride, torch.Tensor.numel, torch.Tensor.__len__,
+    torch.Tensor.is_contiguous, torch.Tensor.data_ptr, torch.Tensor.element_size, torch.Tensor.get_device,
+    torch.Tensor.is_floating_point, torch.Tensor.type,
+    _getter("shape"), _getter("device"), _getter("dtype"), _getter("is_cuda"), _getter("ndim"),
+    _getter("layout"), _getter("requires_grad"), _getter("is_sparse"), _getter("grad"), _getter("grad_fn"),
+    _getter("is_leaf"),
+}
+_IDENTITY = {torch.Tensor.cuda, torch.Tensor.float, torch.Tensor.contiguous, torch.Tensor.detach}
+
+
+class StandardizedFeatures(torch.Tensor):
+    """Raw features + column statistics, semantically equal to ``(raw - mean) / std``."""
+
+    @staticmethod
+    def __new__(cls, raw, mean, std):
+        t = torch.Tensor._make_subclass(cls, raw.detach(), False)
+        t._sgc_mean, t._sgc_std = mean, std
+        return t
+
+    def unwrap(self):
+        with torch._C.DisableTorchFunctionSubclass():
+            return self.as_subclass(torch.Tensor), self._sgc_mean, self._sgc_std
+
+    @staticmethod
+    def materialize(raw, mean, std):
+        """The reference's own expression (utils.py:119) on the GPU, in fp32."""
+        return (raw - mean) / std
+
+    def standardized(self):
+        raw, mean, std = self.unwrap()
+        return StandardizedFeatures.materialize(raw, mean, std)
+
+    @classmethod
+    def __torch_function__(cls, func, types, args=(), kwargs=None):
+        kwargs = kwargs or {}
+        me = args[0] if args and isinstance(args[0], StandardizedFeatures) else None
+        if me is not None and func in _METADATA:
+            with torch._C.DisableTorchFunctionSubclass():
+                return func(*args, **kwargs)
+        if me is not None and func in _IDENTITY:
+            return me
+        if me is not None and func is torch.Tensor.__getitem__ and len(args) == 2 \
+                and not isinstance(args[1], tuple):
+            raw, mean, std = me.unwrap()             # row selection keeps the statistics
+            idx = args[1]
+            if not isinstance(idx, (torch.Tensor, slice, int)):
+                idx = torch.as_tensor(idx, device=raw.device)
+            rows = raw[idx]
+            return StandardizedFeatures(rows, mean, std) if rows.dim() == 2 else (rows - mean) / std
+        # anything else sees the standardised values
+        conv = lambda a: a.standardized() if isinstance(a, StandardizedFeatures) else a
+        args = tuple(conv(a) for a in args)
+        kwargs = {k: conv(v) for k, v in kwargs.items()}
+        with torch._C.DisableTorchFunctionSubclass():
+            return func(*args, **kwargs)

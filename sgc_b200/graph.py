@@ -1,0 +1,300 @@
+"""Device-resident normalised adjacency (the `adj` object of the reference's API).
+
+`SgcGraph` is what `normalization.aug_normalized_adjacency` produces here instead of the scipy COO
+matrix the reference returns (/root/reference/normalization.py:5-12): the canonical CSR structure
+of ``S = D^-1/2 (A+I) D^-1/2`` in HBM together with the fp64 values of ``A+I`` and the fp64
+``D^-1/2`` diagonal.  The normalised values themselves are never stored unless a caller asks for
+the torch / scipy view -- the propagation kernel forms ``fp32((d_i*a_ij)*d_j)`` on the fly.
+
+HBM layout (all contiguous 1-D arrays, 256-byte aligned by the torch allocator):
+    row_ptr  int64 [n+1]     col  int32 [nnz]     aval  float64 [nnz]     dinv  float64 [n]
+
+All arithmetic runs in libsgc_b200.so through sgc_b200._ffi; PyTorch only owns the memory.
+"""
+import weakref
+
+import numpy as np
+import torch
+
+from . import _ffi
+
+_checked_devices = set()
+
+
+def require_cuda(device=None):
+    """Raise unless a B200-class device is usable (no CPU fallback, by design)."""
+    if not torch.cuda.is_available():
+        raise _ffi.SgcError("sgc_b200 needs a CUDA device (sm_100a); it has no CPU fallback -- run the "
+                            "reference implementation for CPU-only (--no-cuda) experiments")
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    if dev.index is None:
+        dev = torch.device("cuda", torch.cuda.current_device())
+    if dev.index not in _checked_devices:
+        _ffi.call("sgc_device_check", dev.index)
+        _checked_devices.add(dev.index)
+    return dev
+
+
+def stream_ptr():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ws(nbytes, device):
+    return torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=device)
+
+
+class SgcGraph(object):
+    """Normalised adjacency S on the GPU (see module docstring).  Treat as opaque: pass it to
+    ``sgc_precompute`` / ``torch.spmm``; ``.to_torch_sparse()`` and ``.tocoo()`` give the views
+    the reference's callers would have had."""
+
+    is_sparse = True
+
+    def __init__(self, n_rows, n_cols, row_ptr, col, aval, dinv, rowsum=None, sval=None):
+        self.n_rows, self.n_cols = int(n_rows), int(n_cols)
+        self.row_ptr, self.col, self.aval, self.dinv, self.rowsum = row_ptr, col, aval, dinv, rowsum
+        self.sval = sval                      # fp32 values of S when materialised (or given)
+        self.nnz = int(col.numel())
+        self.device = row_ptr.device
+        self._plans = {}
+        self._torch_view = None
+
+    # -- shape protocol the reference's callers rely on -----------------------------------
+    @property
+    def shape(self):
+        return (self.n_rows, self.n_cols)
+
+    def size(self, dim=None):
+        return torch.Size(self.shape) if dim is None else self.shape[dim]
+
+    @property
+    def is_cuda(self):
+        return True
+
+    def cuda(self, *a, **k):      # utils.py:84,127-128 call .cuda() on adj: already resident
+        return self
+
+    def float(self):              # utils.py:77,122,124 call .float(): fp32 is what the hop computes in
+        return self
+
+    def to(self, *a, **k):
+        return self
+
+    @property
+    def fused(self):
+        return self.aval is not None and self.dinv is not None
+
+    # -- plan cache --------------------------------------------------------------------------
+    def plan(self, chunk):
+        chunk = max(int(chunk), 0)
+        hit = self._plans.get(chunk)
+        if hit is not None:
+            return hit[0]
+        lib = _ffi.lib()
+        nbytes = lib.sgc_spmm_plan_workspace_bytes(self.n_rows, self.nnz, chunk)
+        ws = _ws(nbytes, self.device)
+        handle = _ffi.c_p()
+        with torch.cuda.device(self.device):
+            _ffi.call("sgc_spmm_plan_create", self.n_rows, self.n_cols, self.nnz, _ffi.ptr(self.row_ptr),
+                      _ffi.ptr(self.col), chunk, _ffi.ptr(ws), ws.numel(), _ffi.ctypes.byref(handle),
+                      stream_ptr())
+        plan = _Plan(handle, ws, int(lib.sgc_spmm_plan_partial_rows(handle)))
+        self._plans[chunk] = (plan,)
+        return plan
+
+    # -- views -------------------------------------------------------------------------------
+    def values32(self):
+        """fp32 values of S: fp32((d_i*a_ij)*d_j), the single rounding of utils.py:25."""
+        if self.sval is None:
+            self.sval = torch.empty(self.nnz, dtype=torch.float32, device=self.device)
+            with torch.cuda.device(self.device):
+                _ffi.call("sgc_norm_build", self.n_rows, _ffi.ptr(self.row_ptr), _ffi.ptr(self.col),
+                          _ffi.ptr(self.aval), _ffi.ptr(self.dinv), _ffi.ptr(self.row_ptr), None, None,
+                          None, _ffi.ptr(self.sval), stream_ptr())
+        return self.sval
+
+    def values64(self):
+        """fp64 values of S as normalization.py:12 returns them."""
+        out = torch.empty(self.nnz, dtype=torch.float64, device=self.device)
+        with torch.cuda.device(self.device):
+            _ffi.call("sgc_norm_build", self.n_rows, _ffi.ptr(self.row_ptr), _ffi.ptr(self.col),
+                      _ffi.ptr(self.aval), _ffi.ptr(self.dinv), _ffi.ptr(self.row_ptr), None, None,
+                      _ffi.ptr(out), None, stream_ptr())
+        return out
+
+    def coo_indices(self):
+        """int64 [2, nnz] row-major sorted indices (utils.py:26-27)."""
+        idx = torch.empty((2, self.nnz), dtype=torch.int64, device=self.device)
+        with torch.cuda.device(self.device):
+            _ffi.call("sgc_csr_to_coo", self.n_rows, _ffi.ptr(self.row_ptr), _ffi.ptr(self.col), self.nnz,
+                      _ffi.ptr(idx), stream_ptr())
+        return idx
+
+    def to_torch_sparse(self):
+        """torch sparse COO fp32 tensor equal to the reference's
+        ``sparse_mx_to_torch_sparse_tensor(aug_normalized_adjacency(adj)).cuda()``."""
+        if self._torch_view is None:
+            self._torch_view = torch.sparse_coo_tensor(self.coo_indices(), self.values32(),
+                                                       torch.Size(self.shape))
+        return self._torch_view
+
+    def tocoo(self):
+        """scipy COO fp64 on the host: the reference's return value of aug_normalized_adjacency."""
+        import scipy.sparse as sp
+        idx = self.coo_indices().cpu().numpy()
+        return sp.coo_matrix((self.values64().cpu().numpy(), (idx[0], idx[1])), shape=self.shape)
+
+    def tocsr(self):
+        return self.tocoo().tocsr()
+
+    # -- torch.spmm(adj, x) keeps working (models.py:38) --------------------------------------
+    @classmethod
+    def __torch_function__(cls, func, types, args=(), kwargs=None):
+        kwargs = kwargs or {}
+        if func in _MATMULS and len(args) == 2 and isinstance(args[0], SgcGraph) \
+                and isinstance(args[1], torch.Tensor) and not kwargs:
+            from .propagate import hop
+            return hop(args[0], args[1])
+        raise TypeError("SgcGraph supports torch.spmm / torch.sparse.mm / torch.mm / torch.matmul with a "
+                        "dense right operand; use .to_torch_sparse() for anything else (got %r)" % (func,))
+
+    def __matmul__(self, other):
+        from .propagate import hop
+        return hop(self, other)
+
+    def __repr__(self):
+        return "SgcGraph(shape=%s, nnz=%d, device=%s, fused_norm=%s)" % (self.shape, self.nnz, self.device,
+                                                                        self.fused)
+
+
+_MATMULS = (torch.spmm, torch.sparse.mm, torch.mm, torch.matmul)
+
+
+class _Plan(object):
+    def __init__(self, handle, ws, partial_rows):
+        self.handle, self.ws, self.partial_rows = handle, ws, partial_rows
+        self._fin = weakref.finalize(self, _ffi.lib().sgc_spmm_plan_destroy, handle)
+
+
+# ---- K1 + K2: normalisation driver ------------------------------------------------------------------
+def normalize_csr(n, row_ptr, col, val):
+    """``aug_normalized_adjacency`` on device CSR arrays (normalization.py:5-12).
+
+    row_ptr int64 [n+1], col int32 [nnz], val float64 [nnz], all on one CUDA device; any stored
+    order (non-canonical input is canonicalised first).  Returns an `SgcGraph`."""
+    dev = require_cuda(row_ptr.device)
+    lib = _ffi.lib()
+    n = int(n)
+    with torch.cuda.device(dev):
+        s = stream_ptr()
+        row_ptr = row_ptr.to(torch.int64).contiguous()
+        col = col.to(torch.int32).contiguous()
+        val = val.to(torch.float64).contiguous()
+        nnz = int(col.numel())
+        scan_ws = _ws(lib.sgc_scan_workspace_bytes(n + 1), dev)
+        flag = torch.empty(1, dtype=torch.int32, device=dev)
+        _ffi.call("sgc_csr_check_canonical", n, n, _ffi.ptr(row_ptr), _ffi.ptr(col), _ffi.ptr(flag), s)
+        if int(flag.item()) == 0:
+            if nnz and (int(col.min().item()) < 0 or int(col.max().item()) >= n):
+                raise ValueError("column index out of range")
+            ws = _ws(lib.sgc_csr_canonicalize_workspace_bytes(n, nnz), dev)
+            rp2 = torch.empty(n + 1, dtype=torch.int64, device=dev)
+            col2 = torch.empty(nnz, dtype=torch.int32, device=dev)
+            val2 = torch.empty(nnz, dtype=torch.float64, device=dev)
+            _ffi.call("sgc_csr_canonicalize", n, nnz, _ffi.ptr(row_ptr), _ffi.ptr(col), _ffi.ptr(val),
+                      _ffi.ptr(rp2), _ffi.ptr(col2), _ffi.ptr(val2), _ffi.ptr(ws), ws.numel(), s)
+            nnz = int(rp2[n].item())
+            row_ptr, col, val = rp2, col2[:nnz], val2[:nnz]
+        # K1: A + I
+        rp_aug = torch.empty(n + 1, dtype=torch.int64, device=dev)
+        _ffi.call("sgc_csr_selfloop_count", n, _ffi.ptr(row_ptr), _ffi.ptr(col), _ffi.ptr(val),
+                  _ffi.ptr(rp_aug), _ffi.ptr(scan_ws), scan_ws.numel(), s)
+        nnz_aug = int(rp_aug[n].item()) if n else 0
+        col_aug = torch.empty(nnz_aug, dtype=torch.int32, device=dev)
+        aval = torch.empty(nnz_aug, dtype=torch.float64, device=dev)
+        _ffi.call("sgc_csr_selfloop_build", n, _ffi.ptr(row_ptr), _ffi.ptr(col), _ffi.ptr(val),
+                  _ffi.ptr(rp_aug), _ffi.ptr(col_aug), _ffi.ptr(aval), s)
+        # K2: degrees
+        rowsum = torch.empty(n, dtype=torch.float64, device=dev)
+        dinv = torch.empty(n, dtype=torch.float64, device=dev)
+        _ffi.call("sgc_degree_inv_sqrt", n, _ffi.ptr(rp_aug), _ffi.ptr(aval), _ffi.ptr(rowsum),
+                  _ffi.ptr(dinv), s)
+        # structure after scipy's zero-product pruning (only differs when some d_i == 0)
+        rp_s = torch.empty(n + 1, dtype=torch.int64, device=dev)
+        dropped = torch.empty(1, dtype=torch.int64, device=dev)
+        _ffi.call("sgc_norm_count", n, _ffi.ptr(rp_aug), _ffi.ptr(col_aug), _ffi.ptr(aval), _ffi.ptr(dinv),
+                  _ffi.ptr(rp_s), _ffi.ptr(dropped), _ffi.ptr(scan_ws), scan_ws.numel(), s)
+        if int(dropped.item()) != 0:
+            nnz_s = int(rp_s[n].item())
+            col_s = torch.empty(nnz_s, dtype=torch.int32, device=dev)
+            aval_s = torch.empty(nnz_s, dtype=torch.float64, device=dev)
+            _ffi.call("sgc_norm_build", n, _ffi.ptr(rp_aug), _ffi.ptr(col_aug), _ffi.ptr(aval),
+                      _ffi.ptr(dinv), _ffi.ptr(rp_s), _ffi.ptr(col_s), _ffi.ptr(aval_s), None, None, s)
+            rp_aug, col_aug, aval = rp_s, col_s, aval_s
+    return SgcGraph(n, n, rp_aug, col_aug, aval, dinv, rowsum=rowsum)
+
+
+def upload_csr(adj, device=None):
+    """scipy sparse matrix (any format/dtype) -> device CSR arrays (row_ptr int64, col int32,
+    val float64).  Host work is limited to scipy's own format conversion; dtype casts run on the
+    device."""
+    import scipy.sparse as sp
+    dev = require_cuda(device)
+    m = adj if sp.issparse(adj) else sp.csr_matrix(adj)
+    if m.format != "csr":
+        m = m.tocsr()
+    if m.shape[0] >= 2 ** 31 or m.shape[1] >= 2 ** 31:
+        raise ValueError("more than 2^31-1 rows/columns are not supported (int32 column indices)")
+    row_ptr = torch.from_numpy(np.ascontiguousarray(m.indptr)).to(dev, non_blocking=False).to(torch.int64)
+    col = torch.from_numpy(np.ascontiguousarray(m.indices)).to(dev).to(torch.int32)
+    data = np.ascontiguousarray(m.data)
+    if data.dtype == np.bool_:
+        data = data.astype(np.uint8)
+    val = torch.from_numpy(data).to(dev).to(torch.float64)
+    return m.shape, row_ptr, col, val
+
+
+def from_scipy(adj, device=None):
+    """normalization.aug_normalized_adjacency on a scipy matrix: upload, then K1/K2 on the GPU."""
+    shape, row_ptr, col, val = upload_csr(adj, device)
+    if shape[0] != shape[1]:
+        raise ValueError("adjacency must be square, got %s" % (shape,))
+    return normalize_csr(shape[0], row_ptr, col, val)
+
+
+def from_torch_sparse(t):
+    """Wrap an existing torch sparse tensor holding S (e.g. one a caller built with the
+    reference's own sparse_mx_to_torch_sparse_tensor and moved to the GPU) without copying its
+    values: zero-copy ingestion of device-resident COO/CSR (scope table row f2)."""
+    dev = require_cuda(t.device)
+    lib = _ffi.lib()
+    with torch.cuda.device(dev):
+        if t.layout == torch.sparse_csr:
+            n_rows, n_cols = t.shape
+            return SgcGraph(n_rows, n_cols, t.crow_indices().to(torch.int64).contiguous(),
+                            t.col_indices().to(torch.int32).contiguous(), None, None,
+                            sval=t.values().to(torch.float32).contiguous())
+        if t.layout != torch.sparse_coo:
+            raise TypeError("expected a torch sparse COO or CSR tensor")
+        n_rows, n_cols = t.shape
+        idx, val = t._indices(), t._values()
+        nnz = int(val.numel())
+        row_ptr = torch.empty(n_rows + 1, dtype=torch.int64, device=dev)
+        col = torch.empty(nnz, dtype=torch.int32, device=dev)
+        flag = torch.empty(1, dtype=torch.int32, device=dev)
+        idx = idx.contiguous()
+        _ffi.call("sgc_coo_to_csr", n_rows, nnz, _ffi.ptr(idx[0]), _ffi.ptr(idx[1]), _ffi.ptr(row_ptr),
+                  _ffi.ptr(col), _ffi.ptr(flag), stream_ptr())
+        if int(flag.item()) == 0:
+            # unsorted or duplicated COO: let torch coalesce (sort + merge) once, then retry
+            tc = t.coalesce()
+            idx, val = tc.indices().contiguous(), tc.values()
+            nnz = int(val.numel())
+            col = torch.empty(nnz, dtype=torch.int32, device=dev)
+            _ffi.call("sgc_coo_to_csr", n_rows, nnz, _ffi.ptr(idx[0]), _ffi.ptr(idx[1]), _ffi.ptr(row_ptr),
+                      _ffi.ptr(col), _ffi.ptr(flag), stream_ptr())
+            if int(flag.item()) == 0:
+                raise _ffi.SgcError("could not convert the sparse tensor to CSR")
+        g = SgcGraph(n_rows, n_cols, row_ptr, col, None, None, sval=val.to(torch.float32).contiguous())
+        g._torch_view = t
+        return g

@@ -1,0 +1,170 @@
+"""K-hop feature propagation  X <- S X  on the GPU (the reference's utils.sgc_precompute,
+/root/reference/utils.py:92-97, whose inner call is torch.spmm).
+
+Data layout in HBM: the caller's feature matrix is row-major fp32 ``[N, F]``.  Intermediate hops
+are written to internal ping-pong buffers with a leading dimension padded to a multiple of 8
+floats (32-byte sectors; e.g. 602 -> 608) so that every gather of a neighbour row is a run of whole
+16-byte vectors; the last hop writes a contiguous ``[N, F]`` result, as the reference returns.
+Only two such buffers exist at any time: no normalised adjacency and no standardised copy of the
+features is materialised.
+"""
+import os
+from time import perf_counter
+
+import torch
+
+from . import _ffi
+from .graph import SgcGraph, from_torch_sparse, require_cuda, stream_ptr
+
+_ENV = os.environ.get
+
+
+def default_chunk():
+    """Rows with more stored entries than this are split (SGC_B200_CHUNK; 0 = never split, i.e.
+    bit-exact sequential accumulation for every row)."""
+    return int(_ENV("SGC_B200_CHUNK", "512"))
+
+
+def default_hints():
+    return int(_ENV("SGC_B200_HINTS", "3"))
+
+
+def default_slab():
+    return int(_ENV("SGC_B200_SLAB", "0"))
+
+
+def default_std_mode():
+    """'div' reproduces utils.py:119 exactly ((x-mean)/std); 'rcp' multiplies by 1/std."""
+    return _ENV("SGC_B200_STD", "div")
+
+
+def _pad8(f):
+    return (f + 7) // 8 * 8
+
+
+def as_graph(adj):
+    if isinstance(adj, SgcGraph):
+        return adj
+    if isinstance(adj, torch.Tensor) and adj.layout in (torch.sparse_coo, torch.sparse_csr):
+        g = getattr(adj, "_sgc_graph", None)
+        if g is None:
+            g = from_torch_sparse(adj)
+            try:
+                adj._sgc_graph = g          # reuse the CSR + plan on the next call
+            except Exception:
+                pass
+        return g
+    raise TypeError("adj must be an SgcGraph or a CUDA torch sparse tensor, got %r" % type(adj))
+
+
+def _hop_args(g, plan, x, ldx, y, ldy, f, partial, mean, std, std_mode, slab, hints):
+    a = _ffi.HopArgs()
+    flags = 0
+    if g.fused:
+        flags |= _ffi.HOP_FUSED_NORM
+        a.aval_d, a.dinv_d = _ffi.ptr(g.aval), _ffi.ptr(g.dinv)
+    else:
+        a.sval_d = _ffi.ptr(g.sval)
+    if mean is not None:
+        flags |= _ffi.HOP_STD_DIV if std_mode == "div" else _ffi.HOP_STD_RCP
+        a.mean_d, a.std_d = _ffi.ptr(mean), _ffi.ptr(std)
+    a.x_d, a.ldx, a.y_d, a.ldy = x, ldx, y, ldy
+    if partial is not None:
+        a.partial_d, a.ldp = _ffi.ptr(partial), partial.stride(0)
+    a.f, a.slab_floats, a.flags, a.hints = f, slab, flags, hints
+    return a
+
+
+def _check_features(g, x):
+    if not isinstance(x, torch.Tensor) or x.dim() != 2:
+        raise TypeError("features must be a 2-D torch tensor")
+    if x.device != g.device:
+        raise ValueError("features are on %s but the graph is on %s" % (x.device, g.device))
+    if x.shape[0] != g.n_cols:
+        raise ValueError("size mismatch: adj is %s, features are %s" % (g.shape, tuple(x.shape)))
+    if x.dtype != torch.float32:
+        x = x.float()
+    if x.stride(1) != 1 or x.stride(0) < x.shape[1]:
+        x = x.contiguous()
+    return x
+
+
+def _partial(plan, f, dev):
+    if plan.partial_rows == 0:
+        return None
+    return torch.empty((plan.partial_rows, (f + 3) // 4 * 4), dtype=torch.float32, device=dev)
+
+
+def hop(adj, x, mean=None, std=None, chunk=None, slab=None, hints=None, std_mode=None, out=None):
+    """One hop ``S @ x`` (torch.spmm(adj, x), utils.py:95).  Returns a new [n_rows, F] fp32
+    tensor.  With ``mean``/``std`` (fp32 [F]) the gathered operand is standardised on the fly."""
+    g = as_graph(adj)
+    dev = require_cuda(g.device)
+    x = _check_features(g, x)
+    f = int(x.shape[1])
+    if mean is not None:
+        mean, std = mean.to(dev, torch.float32).contiguous(), std.to(dev, torch.float32).contiguous()
+    with torch.cuda.device(dev):
+        y = out if out is not None else torch.empty((g.n_rows, f), dtype=torch.float32, device=dev)
+        if f == 0 or g.n_rows == 0:
+            return y
+        plan = g.plan(default_chunk() if chunk is None else chunk)
+        partial = _partial(plan, f, dev)
+        a = _hop_args(g, plan, x.data_ptr(), x.stride(0), y.data_ptr(), y.stride(0), f, partial, mean, std,
+                      std_mode or default_std_mode(), default_slab() if slab is None else slab,
+                      default_hints() if hints is None else hints)
+        _ffi.call("sgc_spmm_hop", plan.handle, _ffi.ctypes.byref(a), stream_ptr())
+    return y
+
+
+def propagate(adj, x, degree, mean=None, std=None, chunk=None, slab=None, hints=None, std_mode=None):
+    """K hops, stream-ordered, no synchronisation; returns the [N, F] fp32 result tensor."""
+    g = as_graph(adj)
+    dev = require_cuda(g.device)
+    degree = int(degree)
+    if degree <= 0:
+        return x
+    if g.n_rows != g.n_cols:
+        raise ValueError("K-hop propagation needs a square adjacency, got %s" % (g.shape,))
+    x = _check_features(g, x)
+    n, f = int(x.shape[0]), int(x.shape[1])
+    if mean is not None:
+        mean, std = mean.to(dev, torch.float32).contiguous(), std.to(dev, torch.float32).contiguous()
+    with torch.cuda.device(dev):
+        y = torch.empty((n, f), dtype=torch.float32, device=dev)
+        if f == 0 or n == 0:
+            return y
+        plan = g.plan(default_chunk() if chunk is None else chunk)
+        partial = _partial(plan, f, dev)
+        ld = _pad8(f)
+        bufs = []
+        for _ in range(min(degree - 1, 2)):
+            b = torch.empty((n, ld), dtype=torch.float32, device=dev)
+            if ld != f:
+                b[:, f:].zero_()
+            bufs.append(b)
+        a = _hop_args(g, plan, x.data_ptr(), x.stride(0), y.data_ptr(), y.stride(0), f, partial, mean, std,
+                      std_mode or default_std_mode(), default_slab() if slab is None else slab,
+                      default_hints() if hints is None else hints)
+        _ffi.call("sgc_precompute", plan.handle, _ffi.ctypes.byref(a), degree,
+                  _ffi.ptr(bufs[0]) if bufs else None, _ffi.ptr(bufs[1]) if len(bufs) > 1 else None, ld,
+                  stream_ptr())
+    return y
+
+
+def sgc_precompute(features, adj, degree, **kw):
+    """Drop-in for utils.sgc_precompute (utils.py:92-97): returns ``(features, seconds)``.
+    Unlike the reference, the clock is read after the stream has drained, so the time is the
+    real duration of the K hops."""
+    from .features import StandardizedFeatures
+    if int(degree) <= 0:
+        return features, 0.0            # utils.py:94: the loop does not run; same object back
+    mean = std = None
+    if isinstance(features, StandardizedFeatures):
+        features, mean, std = features.unwrap()
+    g = as_graph(adj)
+    torch.cuda.synchronize(g.device)
+    t = perf_counter()
+    out = propagate(g, features, degree, mean=mean, std=std, **kw)
+    torch.cuda.synchronize(g.device)
+    return out, perf_counter() - t

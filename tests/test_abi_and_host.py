@@ -1,0 +1,197 @@
+"""CPU-only checks: the C-ABI library loads and exports every symbol include/sgc_b200.h declares,
+the ctypes mirror of its structs matches the C layout, the host-side API mirrors the reference's
+names and signatures, and there is no CPU fallback."""
+import ctypes
+import inspect
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = os.path.join(REPO, "include", "sgc_b200.h")
+REFERENCE = "/root/reference"
+
+
+def declared_symbols():
+    text = open(HEADER).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(sgc_[a-z0-9_]+)\s*\(", text)))
+
+
+@pytest.fixture(scope="module")
+def built():
+    import __graft_entry__ as entry
+    entry.build()
+    from sgc_b200 import _ffi
+    return _ffi
+
+
+def test_library_exports_every_declared_symbol(built):
+    names = declared_symbols()
+    assert len(names) >= 20
+    handle = ctypes.CDLL(built.LIB_PATH)
+    for name in names:
+        assert hasattr(handle, name), "libsgc_b200.so does not export %s" % name
+    # and the ctypes table binds exactly the declared surface
+    assert sorted(built.SIGNATURES) == names
+    assert built.lib().sgc_version().decode().startswith("sgc_b200")
+
+
+def test_library_is_sm100a_only(built):
+    out = subprocess.run(["cuobjdump", "-lelf", built.LIB_PATH], capture_output=True, text=True)
+    if out.returncode != 0:
+        pytest.skip("cuobjdump unavailable")
+    archs = set(re.findall(r"sm_\d+a?", out.stdout))
+    assert archs == {"sm_100a"}, archs
+
+
+def test_hop_args_layout_matches_c(built, tmp_path):
+    src = tmp_path / "layout.c"
+    src.write_text(
+        '#include <stdio.h>\n#include <stddef.h>\n#include "sgc_b200.h"\n'
+        "int main(void){printf(\"%zu\", sizeof(sgc_hop_args_t));\n"
+        + "".join('printf(" %%zu", offsetof(sgc_hop_args_t, %s));\n' % f for f in
+                  ["aval_d", "dinv_d", "sval_d", "x_d", "ldx", "y_d", "ldy", "partial_d", "ldp", "mean_d",
+                   "std_d", "f", "slab_floats", "flags", "hints"])
+        + "return 0;}\n")
+    exe = tmp_path / "layout"
+    subprocess.check_call(["gcc", "-I", os.path.join(REPO, "include"), str(src), "-o", str(exe)])
+    nums = [int(v) for v in subprocess.check_output([str(exe)]).split()]
+    assert nums[0] == ctypes.sizeof(built.HopArgs)
+    got = [getattr(built.HopArgs, name).offset for name, _ in built.HopArgs._fields_]
+    assert nums[1:] == got
+
+
+def test_host_calls_validate_arguments_without_a_gpu(built):
+    lib = built.lib()
+    assert lib.sgc_scan_workspace_bytes(1 << 20) > 0
+    assert lib.sgc_spmm_plan_workspace_bytes(1000, 5000, 0) > 0
+    assert lib.sgc_spmm_plan_workspace_bytes(1000, 5000, 64) > lib.sgc_spmm_plan_workspace_bytes(1000, 5000, 0)
+    rc = lib.sgc_spmm_hop(None, None, None)
+    assert rc == -1 and b"null" in lib.sgc_last_error()
+    with pytest.raises(built.SgcError):
+        built.check(rc, "sgc_spmm_hop")
+
+
+@pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU behaviour")
+def test_no_cpu_fallback():
+    import sgc_b200
+    import scipy.sparse as sp
+    from sgc_b200 import _ffi
+    with pytest.raises(_ffi.SgcError):
+        sgc_b200.aug_normalized_adjacency(sp.eye(4, format="csr"))
+    import utils as drop_in
+    with pytest.raises(_ffi.SgcError):
+        drop_in.load_citation("cora", "AugNormAdj", False)
+    with pytest.raises(_ffi.SgcError):
+        drop_in.load_reddit_data("AugNormAdj", cuda=False)
+    sparse = torch.sparse_coo_tensor(torch.tensor([[0, 1], [1, 0]]), torch.ones(2), (2, 2))
+    with pytest.raises(_ffi.SgcError):
+        drop_in.sgc_precompute(torch.ones(2, 3), sparse, 2)
+    same, secs = drop_in.sgc_precompute(sparse, sparse, 0)      # degree 0: loop does not run
+    assert same is sparse and secs == 0.0
+
+
+def test_product_does_not_import_the_oracle():
+    """Nothing under sgc_b200/ (nor the drop-in shims) may import, call or link the oracle."""
+    offenders = []
+    files = [os.path.join(REPO, "utils.py"), os.path.join(REPO, "normalization.py")]
+    for root, _, names in os.walk(os.path.join(REPO, "sgc_b200")):
+        files += [os.path.join(root, n) for n in names if n.endswith((".py", ".cu", ".cuh", ".h", "Makefile"))]
+    for path in files:
+        text = open(path).read()
+        if re.search(r"^\s*(from|import)\s+oracle\b|liboracle|oracle/", text, flags=re.M):
+            offenders.append(path)
+    assert not offenders, offenders
+
+
+@pytest.mark.skipif(not os.path.isdir(REFERENCE), reason="reference tree not present on this machine")
+def test_api_mirrors_reference_signatures():
+    """Same public names, parameter names, order and defaults as the reference's modules
+    (utils.py / normalization.py), checked by loading the reference's source under another name."""
+    import importlib.util
+    import normalization as mine_norm
+    import utils as mine_utils
+
+    def load(name, alias):
+        # the reference's utils does `from normalization import ...`: resolve it to the reference's
+        sys.path.insert(0, REFERENCE)
+        saved = {k: sys.modules.pop(k) for k in ("normalization", "utils") if k in sys.modules}
+        try:
+            spec = importlib.util.spec_from_file_location(alias, os.path.join(REFERENCE, name + ".py"))
+            mod = importlib.util.module_from_spec(spec)
+            spec.loader.exec_module(mod)
+            return mod
+        finally:
+            sys.path.remove(REFERENCE)
+            for k in ("normalization", "utils"):
+                sys.modules.pop(k, None)
+            sys.modules.update(saved)
+
+    ref_norm, ref_utils = load("normalization", "_ref_normalization"), load("utils", "_ref_utils")
+    for ref, mine, names in (
+            (ref_norm, mine_norm, ["aug_normalized_adjacency", "fetch_normalization", "row_normalize"]),
+            (ref_utils, mine_utils, ["sgc_precompute", "load_citation", "load_reddit_data",
+                                     "sparse_mx_to_torch_sparse_tensor", "preprocess_citation",
+                                     "parse_index_file", "set_seed", "loadRedditFromNPZ",
+                                     "fetch_normalization", "row_normalize"])):
+        for name in names:
+            a, b = inspect.signature(getattr(ref, name)), inspect.signature(getattr(mine, name))
+            pa = [(p.name, p.default) for p in a.parameters.values()]
+            pb = [(p.name, p.default) for p in b.parameters.values() if p.kind != p.VAR_KEYWORD]
+            assert pa == pb, (name, pa, pb)
+    # unknown normalisation: a zero-argument callable, like the reference
+    assert mine_norm.fetch_normalization("NoSuch")() == ref_norm.fetch_normalization("NoSuch")()
+
+
+@pytest.mark.skipif(not os.path.isdir(os.path.join(REFERENCE, "data")), reason="reference data not present")
+def test_planetoid_adjacency_matches_reference_loader():
+    import pickle
+    from conftest import load_golden
+    from sgc_b200 import utils as mine
+    for ds in ("cora", "citeseer", "pubmed"):
+        with open(os.path.join(REFERENCE, "data", "ind.%s.graph" % ds), "rb") as fh:
+            graph = pickle.load(fh, encoding="latin1")
+        adj = mine._planetoid_adjacency(graph)
+        g = load_golden(ds)
+        assert np.array_equal(adj.indptr, g["adj_indptr"]) and np.array_equal(adj.indices, g["adj_indices"])
+        assert np.array_equal(adj.data.astype(np.float64), g["adj_data"])
+
+
+def test_row_normalize_matches_golden():
+    import scipy.sparse as sp
+    from conftest import load_golden
+    import normalization as mine
+    for ds, f in (("cora", 1433), ("citeseer", 3703)):
+        g = load_golden(ds)
+        n = g["featraw_indptr"].size - 1
+        raw = sp.csr_matrix((g["featraw_data"], g["featraw_indices"], g["featraw_indptr"]), shape=(n, f))
+        out = sp.csr_matrix(mine.row_normalize(raw))
+        out.sort_indices()
+        out.eliminate_zeros()
+        assert np.array_equal(out.indices, g["featnorm_indices"])
+        assert np.array_equal(out.data.astype(np.float32), g["featnorm_data"].astype(np.float32))
+
+
+def test_standardized_features_semantics():
+    from sgc_b200.features import StandardizedFeatures
+    torch.manual_seed(0)
+    raw = torch.randn(50, 7) * 3 + 2
+    mean, std = raw.mean(0), raw.std(0)
+    feats = StandardizedFeatures(raw, mean, std)
+    ref = (raw - mean) / std                                  # utils.py:119
+    assert feats.size(1) == 7 and feats.shape == ref.shape and len(feats) == 50
+    idx = np.array([3, 1, 40])
+    sub = feats[idx]                                          # reddit.py:45 indexes with ndarrays
+    assert isinstance(sub, StandardizedFeatures) and torch.equal(sub.standardized(), ref[idx])
+    lin = torch.nn.Linear(7, 3)
+    assert torch.equal(lin(feats), lin(ref))                  # any torch op sees standardised values
+    assert torch.equal(feats * 1.0, ref) and type(feats * 1.0) is torch.Tensor
+    assert feats.cuda is not None and feats.float() is feats
+    rawt, m, s = feats.unwrap()
+    assert type(rawt) is torch.Tensor and rawt.data_ptr() == raw.data_ptr() and m is mean and s is std

@@ -1,0 +1,312 @@
+"""Parity of the CUDA path (through the C ABI) against the CPU oracle and the reference's golden
+vectors.  Integer / index work must be bit-exact; fp32 propagation is bit-exact for rows that are
+not split and within |a-b| <= 1e-6 + 1e-5*|b| (north_star's tolerance) for split rows."""
+import hashlib
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import load_golden
+
+pytestmark = pytest.mark.gpu
+
+RTOL, ATOL = 1e-5, 1e-6
+
+
+def sha(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+@pytest.fixture(scope="module")
+def dev():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    import sgc_b200  # noqa: F401  (fails loudly if libsgc_b200.so is missing)
+    from sgc_b200 import _ffi
+    _ffi.lib()
+    return torch.device("cuda", 0)
+
+
+def to_dev(a, dev):
+    return torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+
+
+def gpu_graph(g, dev, prefix="adj"):
+    import sgc_b200
+    n = g[prefix + "_indptr"].size - 1
+    return sgc_b200.normalize_csr(n, to_dev(g[prefix + "_indptr"], dev), to_dev(g[prefix + "_indices"], dev),
+                                  to_dev(g[prefix + "_data"], dev))
+
+
+def coo_rows(graph):
+    rp = graph.row_ptr.cpu().numpy()
+    return np.repeat(np.arange(rp.size - 1, dtype=np.int64), np.diff(rp))
+
+
+def ulp64(a, b):
+    return np.abs(a.view(np.int64) - b.view(np.int64)).max() if a.size else 0
+
+
+# ---- K1 / K2 -------------------------------------------------------------------------------------
+@pytest.mark.parametrize("ds", ["cora", "citeseer", "pubmed", "textsgc_block"])
+def test_normalisation_matches_reference(dev, ds):
+    g = load_golden(ds)
+    graph = gpu_graph(g, dev)
+    assert np.array_equal(coo_rows(graph), g["S_row"])                       # row_ptr bit-exact
+    assert np.array_equal(graph.col.cpu().numpy().astype(np.int64), g["S_col"])   # col_idx bit-exact
+    s64 = graph.values64().cpu().numpy()
+    # fp64 values: the reference's own pow() is host-dependent in the last bit (glibc vs SVML)
+    assert ulp64(s64, g["S_data64"]) <= 2
+    if "S_val32_sha" in g.files:
+        assert sha(graph.values32().cpu().numpy()) == str(g["S_val32_sha"])   # the fp32 S the reference feeds torch.spmm
+        idx = graph.coo_indices().cpu().numpy()
+        assert sha(idx) == str(g["S_idx_sha"])                                # int64 [2,nnz] of utils.py:26-27
+    # against the oracle restatement as well (same inputs)
+    from oracle import normalization_oracle as no
+    n = g["adj_indptr"].size - 1
+    r = no.aug_normalized_adjacency_oracle(n, g["adj_indptr"], g["adj_indices"], g["adj_data"])
+    assert np.array_equal(graph.row_ptr.cpu().numpy(), r["indptr"])
+    assert np.array_equal(graph.rowsum.cpu().numpy().view(np.int64), r["row_sum"].view(np.int64))
+    assert ulp64(graph.dinv.cpu().numpy(), r["d"]) <= 1
+
+
+def test_normalisation_edge_cases(dev):
+    import sgc_b200
+    g = load_golden("edge_cases")
+    for name in [str(x) for x in g["names"]]:
+        n = int(g[name + "/n"])
+        graph = sgc_b200.normalize_csr(n, to_dev(g[name + "/in_indptr"], dev), to_dev(g[name + "/in_indices"], dev),
+                                       to_dev(g[name + "/in_data"], dev))
+        order = np.lexsort((g[name + "/S_col"], g[name + "/S_row"]))
+        assert np.array_equal(coo_rows(graph), g[name + "/S_row"][order]), name
+        assert np.array_equal(graph.col.cpu().numpy().astype(np.int64), g[name + "/S_col"][order]), name
+        got, ref = graph.values64().cpu().numpy(), g[name + "/S_data"][order]
+        assert np.array_equal(np.isnan(got), np.isnan(ref)), name
+        ok = ~np.isnan(ref)
+        if name == "non_canonical":
+            assert np.allclose(got[ok], ref[ok], rtol=1e-15, atol=0), name
+        else:
+            assert ulp64(got[ok], ref[ok]) <= 2, name
+
+
+def test_scipy_entry_point(dev):
+    """normalization.aug_normalized_adjacency on a scipy matrix == the golden reference output,
+    and .tocoo() hands back the reference's return type."""
+    import scipy.sparse as sp
+    import normalization as drop_in
+    g = load_golden("citeseer")
+    n = g["adj_indptr"].size - 1
+    adj = sp.csr_matrix((g["adj_data"], g["adj_indices"], g["adj_indptr"]), shape=(n, n))
+    S = drop_in.fetch_normalization("AugNormAdj")(adj)
+    coo = S.tocoo()
+    assert sp.isspmatrix_coo(coo) and coo.dtype == np.float64
+    assert np.array_equal(coo.row, g["S_row"]) and np.array_equal(coo.col, g["S_col"])
+    assert ulp64(coo.data, g["S_data64"]) <= 2
+    import utils as drop_utils
+    t = drop_utils.sparse_mx_to_torch_sparse_tensor(S)
+    assert t.is_sparse and t.dtype == torch.float32 and t._indices().dtype == torch.int64
+    assert sha(t._values().cpu().numpy()) == str(g["S_val32_sha"])
+    with pytest.raises(TypeError):
+        drop_in.fetch_normalization("FirstOrderGCN")(adj)      # same failure mode as the reference
+
+
+# ---- K4 ------------------------------------------------------------------------------------------
+def dense_features(g):
+    n = g["featnorm_indptr"].size - 1
+    f = {2708: 1433, 3327: 3703}[n]
+    x = np.zeros((n, f), dtype=np.float32)
+    rows = np.repeat(np.arange(n), np.diff(g["featnorm_indptr"]))
+    x[rows, g["featnorm_indices"]] = g["featnorm_data"].astype(np.float32)
+    return x
+
+
+@pytest.mark.parametrize("ds", ["cora", "citeseer"])
+def test_precompute_bit_exact_citation(dev, ds):
+    import sgc_b200
+    g = load_golden(ds)
+    graph = gpu_graph(g, dev)
+    x = dense_features(g)
+    assert sha(x) == str(g["X_sha"])
+    xd = to_dev(x, dev)
+    y1, _ = sgc_b200.sgc_precompute(xd, graph, 1)
+    assert sha(y1.cpu().numpy()) == str(g["Y1_sha"])
+    y2, secs = sgc_b200.sgc_precompute(xd, graph, 2)
+    assert secs > 0 and y2.shape == xd.shape and y2.is_contiguous()
+    assert sha(y2.cpu().numpy()) == str(g["Y_sha"])            # == reference torch.spmm bytes
+    y0, _ = sgc_b200.sgc_precompute(xd, graph, 0)
+    assert y0 is xd
+    # the materialised-S path (torch sparse tensor in, as a reference caller would pass)
+    st = graph.to_torch_sparse()
+    y2b, _ = sgc_b200.sgc_precompute(xd, st, 2)
+    assert sha(y2b.cpu().numpy()) == str(g["Y_sha"])
+    # torch.spmm(adj, x) dispatches to the same kernel (models.py:38)
+    assert torch.equal(torch.spmm(graph, xd), y1)
+
+
+def test_precompute_bit_exact_pubmed_all_slabs(dev):
+    import sgc_b200
+    from sgc_b200 import synth
+    g = load_golden("pubmed")
+    graph = gpu_graph(g, dev)
+    x = synth.tfidf_features(19717, 500, density=0.1, seed=1)
+    assert sha(x.numpy()) == str(g["X_sha"])
+    xd = x.to(dev)
+    for slab in (0, 32, 64, 128, 256):
+        for hints in (0, 3):
+            y, _ = sgc_b200.sgc_precompute(xd, graph, 2, slab=slab, hints=hints)
+            assert sha(y.cpu().numpy()) == str(g["Y_sha"]), (slab, hints)
+
+
+@pytest.mark.parametrize("f", [1, 3, 30, 100, 128, 257, 602])
+@pytest.mark.parametrize("k", [1, 2, 3])
+def test_precompute_alignment_cases(dev, f, k):
+    """Feature widths with 4-, 8- and 16-byte aligned rows, partial slabs, K up to 3 -- bit-exact
+    against the oracle's sequential-FMA loop."""
+    import sgc_b200
+    from oracle import spmm_oracle as so
+    g = load_golden("cora")
+    graph = gpu_graph(g, dev)
+    rng = np.random.RandomState(f * 10 + k)
+    x = rng.standard_normal((2708, f)).astype(np.float32)
+    want, _ = so.sgc_precompute_oracle(x, graph.row_ptr.cpu().numpy(), graph.col.cpu().numpy(),
+                                       graph.values32().cpu().numpy(), k)
+    for slab in (0, 32, 64):
+        y, _ = sgc_b200.sgc_precompute(to_dev(x, dev), graph, k, slab=slab)
+        assert np.array_equal(y.cpu().numpy(), want), (f, k, slab)
+
+
+def powerlaw_case(dev, scale=0.02, seed=3):
+    import sgc_b200
+    from sgc_b200 import synth
+    s = synth.make_shape("reddit", device=dev, scale=scale, seed=seed)
+    graph = sgc_b200.normalize_csr(s["n"], s["row_ptr"], s["col"], s["val"])
+    return s, graph
+
+
+def test_long_rows_split_and_exact_mode(dev):
+    """Power-law graph with hub rows far longer than the split threshold: exact mode (chunk=0) is
+    bit-identical to the oracle; the split path stays within north_star's tolerance and is
+    deterministic."""
+    import sgc_b200
+    from oracle import spmm_oracle as so
+    s, graph = powerlaw_case(dev)
+    rp, col, val = graph.row_ptr.cpu().numpy(), graph.col.cpu().numpy(), graph.values32().cpu().numpy()
+    assert np.diff(rp).max() > 600
+    x = s["x"][:, :96].contiguous()
+    want, _ = so.sgc_precompute_oracle(x.cpu().numpy(), rp, col, val, 2)
+    exact, _ = sgc_b200.sgc_precompute(x, graph, 2, chunk=0)
+    assert np.array_equal(exact.cpu().numpy(), want)
+    for chunk in (64, 512):
+        a, _ = sgc_b200.sgc_precompute(x, graph, 2, chunk=chunk)
+        b, _ = sgc_b200.sgc_precompute(x, graph, 2, chunk=chunk)
+        assert torch.equal(a, b)                                         # run-to-run deterministic
+        assert np.allclose(a.cpu().numpy(), want, rtol=RTOL, atol=ATOL)
+        assert graph.plan(chunk).partial_rows > 0
+
+
+def test_fused_standardisation(dev):
+    """First-hop standardisation fused into the gather == the oracle's hop on (x-mean)/std with the
+    same fp32 statistics (DIV mode bit-exact; RCP mode within tolerance); statistics themselves
+    against the oracle's fp64 column statistics."""
+    import sgc_b200
+    from oracle import spmm_oracle as so
+    s, graph = powerlaw_case(dev, scale=0.01, seed=5)
+    x = s["x"][:, :130].contiguous()
+    mean32, std32, mean64, std64 = sgc_b200.col_stats(x, want64=True)
+    om, osd = so.col_stats(x.cpu().numpy())
+    assert np.allclose(mean64.cpu().numpy(), om, rtol=1e-12, atol=1e-12)
+    assert np.allclose(std64.cpu().numpy(), osd, rtol=1e-12, atol=0)
+    # torch's own fp32 statistics (what utils.py:119 computes) agree to fp32 rounding
+    assert torch.allclose(mean32, x.mean(0), rtol=1e-5, atol=1e-6)
+    assert torch.allclose(std32, x.std(0), rtol=1e-5, atol=0)
+    rp, col, val = graph.row_ptr.cpu().numpy(), graph.col.cpu().numpy(), graph.values32().cpu().numpy()
+    m, sd = mean32.cpu().numpy(), std32.cpu().numpy()
+    want = so.spmm_hop(rp, col, val, x.cpu().numpy(), mean=m, std=sd)
+    got = sgc_b200.hop(graph, x, mean=mean32, std=std32, chunk=0, std_mode="div")
+    assert np.array_equal(got.cpu().numpy(), want)
+    got_rcp = sgc_b200.hop(graph, x, mean=mean32, std=std32, chunk=0, std_mode="rcp")
+    assert np.allclose(got_rcp.cpu().numpy(), want, rtol=RTOL, atol=ATOL)
+    # through the public API: StandardizedFeatures in, two hops out
+    feats = sgc_b200.StandardizedFeatures(x, mean32, std32)
+    y, _ = sgc_b200.sgc_precompute(feats, graph, 2, chunk=0)
+    want2 = so.spmm_hop(rp, col, val, want)
+    assert np.array_equal(y.cpu().numpy(), want2)
+    sub = feats[np.arange(0, 50)]
+    assert isinstance(sub, sgc_b200.StandardizedFeatures)
+    assert torch.equal(sub.standardized(), ((x - mean32) / std32)[:50])
+
+
+def test_downstream_accuracy_unchanged(dev):
+    """Cora / Citeseer: the reference's own training loop (citation.py:35-62, restated here as test
+    code, CPU, seed 42, tuned weight decay) on the GPU-propagated features gives the reference's
+    validation / test accuracy."""
+    import sgc_b200
+    import torch.nn.functional as F
+    for ds in ("cora", "citeseer"):
+        g = load_golden(ds)
+        graph = gpu_graph(g, dev)
+        y, _ = sgc_b200.sgc_precompute(to_dev(dense_features(g), dev), graph, 2)
+        y = y.cpu()
+        labels = torch.from_numpy(g["labels"])
+        tr, va, te = (torch.from_numpy(g[k]) for k in ("idx_train", "idx_val", "idx_test"))
+        torch.manual_seed(42)
+        np.random.seed(42)
+        model = torch.nn.Linear(y.shape[1], int(labels.max()) + 1)
+        # the reference wraps the layer as SGC.W (models.py:7-18); parameter init order is identical
+        opt = torch.optim.Adam(model.parameters(), lr=0.2, weight_decay=float(g["weight_decay"]))
+        for _ in range(int(g["epochs"])):
+            model.train()
+            opt.zero_grad()
+            F.cross_entropy(model(y[tr]), labels[tr]).backward()
+            opt.step()
+        model.eval()
+        with torch.no_grad():
+            acc = lambda idx: (model(y[idx]).max(1)[1] == labels[idx]).double().mean().item()
+            assert abs(acc(va) - float(g["acc_val"])) < 1e-12, ds
+            assert abs(acc(te) - float(g["acc_test"])) < 1e-12, ds
+
+
+def test_full_size_reddit_shape_properties(dev):
+    """BASELINE configs[2] at full size (232,965 nodes, ~23M nnz, 602 features, K=2): size-
+    independent checks -- S.1 equals the row sums of S, linearity of the hop, and the oracle on a
+    random sample of output rows."""
+    import sgc_b200
+    from sgc_b200 import synth
+    from oracle import spmm_oracle as so
+    s = synth.make_shape("reddit", device=dev)
+    graph = sgc_b200.normalize_csr(s["n"], s["row_ptr"], s["col"], s["val"])
+    n, f = s["n"], s["f"]
+    assert graph.nnz > 20_000_000
+    x = s["x"]
+    mean, std = sgc_b200.col_stats(x)
+    y1 = sgc_b200.hop(graph, x, mean=mean, std=std)
+    # (1) S.1 = row sums of S
+    ones = torch.ones((n, 8), dtype=torch.float32, device=dev)
+    rs = sgc_b200.hop(graph, ones)
+    rows = torch.repeat_interleave(torch.arange(n, device=dev), graph.row_ptr[1:] - graph.row_ptr[:-1])
+    want_rs = torch.zeros(n, dtype=torch.float64, device=dev).index_add_(0, rows, graph.values32().double())
+    assert torch.allclose(rs[:, 0].double(), want_rs, rtol=1e-5, atol=1e-6)
+    # (2) linearity: S(2a - b) = 2 S a - S b  (up to fp32 rounding of the three results)
+    a, b = x[:, :64].contiguous(), x[:, 64:128].contiguous()
+    lhs = sgc_b200.hop(graph, 2 * a - b)
+    rhs = 2 * sgc_b200.hop(graph, a) - sgc_b200.hop(graph, b)
+    assert torch.allclose(lhs, rhs, rtol=1e-4, atol=1e-4)
+    # (3) oracle on 1500 sampled rows of hop 1 (fused standardisation) and hop 2
+    rng = np.random.RandomState(0)
+    pick = np.sort(rng.choice(n, 1500, replace=False))
+    rp = graph.row_ptr.cpu().numpy()
+    col, val = graph.col.cpu().numpy(), graph.values32().cpu().numpy()
+    sub_ptr = np.zeros(pick.size + 1, dtype=np.int64)
+    np.cumsum(rp[pick + 1] - rp[pick], out=sub_ptr[1:])
+    take = np.concatenate([np.arange(rp[i], rp[i + 1]) for i in pick])
+    want1 = so.spmm_hop(sub_ptr, col[take], val[take], x.cpu().numpy(), mean=mean.cpu().numpy(),
+                        std=std.cpu().numpy())
+    assert np.allclose(y1.cpu().numpy()[pick], want1, rtol=RTOL, atol=ATOL)
+    y2 = sgc_b200.hop(graph, y1)
+    want2 = so.spmm_hop(sub_ptr, col[take], val[take], y1.cpu().numpy())
+    assert np.allclose(y2.cpu().numpy()[pick], want2, rtol=RTOL, atol=ATOL)
+    # (4) the K-hop entry point agrees with hop-by-hop
+    feats = sgc_b200.StandardizedFeatures(x, mean, std)
+    yk, secs = sgc_b200.sgc_precompute(feats, graph, 2)
+    assert torch.equal(yk, y2) and secs > 0
