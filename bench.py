@@ -1,0 +1,393 @@
+#!/usr/bin/env python
+"""Benchmark of the SGC feature-propagation hot path (BASELINE.json metric: K-hop propagation
+edge*feat/s and achieved HBM GB/s vs roofline).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload NAME]
+
+One "step" = one `sgc_precompute` (K hops of S X with the D^-1/2 scaling and, for the Reddit
+shape, the feature standardisation fused into the first hop) on synthetic inputs of the named
+BASELINE shape.  N=1 workload: configs[2], the Reddit-shaped graph (232,965 nodes, ~23M nnz,
+602 features, K=2) -- the configuration north_star's roofline target is quoted on.  Prints ONE
+JSON line (rank 0).  See DESIGN.md "Measurement" for the definitions of every key.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+from sgc_b200 import synth  # noqa: E402
+
+METRIC = "K-hop propagation edge*feat/s (sgc_precompute)"
+UNIT = "edge*feat/s"
+
+
+def env_int(name, default):
+    return int(os.environ.get(name, default))
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as fh:
+            return float(json.load(fh)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def ncu_traffic(workload):
+    """dram bytes per hop launch from the committed ncu --set full capture, if there is one."""
+    path = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+    if os.path.exists(path):
+        with open(path) as fh:
+            return json.load(fh).get(workload)
+    return None
+
+
+def hop_bytes(n, nnz, f):
+    """Algorithmic bytes of one hop, gather model (SURVEY.md 8d / DESIGN.md): per stored entry one
+    int32 column, one fp32 weight and one F-float row of X; per row one F-float store and one
+    int64 row pointer."""
+    return nnz * (4 + 4 + 4 * f) + 4 * f * n + 8 * (n + 1)
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons through NVML while the timed region runs."""
+
+    def __init__(self, index, period=0.02):
+        super().__init__(daemon=True)
+        self.index, self.period = index, period
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._halt = threading.Event()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            visible = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(visible.split(",")[index]) if visible and visible.split(",")[index].isdigit() else index
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        names = {
+            "hw_slowdown": nv.nvmlClocksEventReasonHwSlowdown if hasattr(nv, "nvmlClocksEventReasonHwSlowdown") else 0x8,
+            "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20, "sw_power_cap": 0x4,
+            "hw_power_brake_slowdown": 0x80,
+        }
+        while not self._halt.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    mask = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for k, bit in names.items():
+                    if mask & bit:
+                        self.reasons.add(k)
+            except Exception:
+                pass
+            time.sleep(self.period)
+
+    def stop(self):
+        self._halt.set()
+        self.join(timeout=2)
+        return {"sm_mhz": float(np.median(self.samples)) if self.samples else None,
+                "sm_max_mhz": float(self.max_mhz) if self.max_mhz else None,
+                "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+def make_workload(name, device, scale=1.0):
+    s = synth.make_shape(name, device=device, scale=scale)
+    return s
+
+
+# --------------------------------------------------------------------------------------------------
+def cpu_reference_rate(s_csr_host, x_host, mean, std, rows, reps, threads):
+    """The reference's own CPU implementation of the path (oracle/reference_port.py: torch.spmm on
+    a torch sparse tensor built like utils.py:23-30) on the first `rows` rows of S; returns
+    (edge*feat/s, seconds per rep, nnz in the sample)."""
+    from oracle import reference_port as rp
+    import scipy.sparse as sp
+    torch.set_num_threads(threads)
+    indptr, indices, data = s_csr_host
+    sub = sp.csr_matrix((data[:indptr[rows]], indices[:indptr[rows]], indptr[:rows + 1]),
+                        shape=(rows, x_host.shape[0]))
+    adj = rp.sparse_mx_to_torch_sparse_tensor(sub)
+    x = torch.from_numpy(x_host)
+    if mean is not None:
+        x = (x - torch.from_numpy(mean)) / torch.from_numpy(std)      # utils.py:119 (outside the timed hops)
+    rp.sgc_precompute(x, adj, 1)                                       # warm-up
+    best = []
+    for _ in range(reps):
+        _, secs = rp.sgc_precompute(x, adj, 1)
+        best.append(secs)
+    secs = float(np.median(best))
+    nnz = int(indptr[rows])
+    return nnz * x_host.shape[1] / secs, secs, nnz
+
+
+def host_copies(graph, x):
+    """Host (pinned) copies of S in CSR fp32 and of X, for the CPU arms."""
+    indptr = graph.row_ptr.cpu().numpy()
+    indices = graph.col.cpu().numpy()
+    data = graph.values32().cpu().numpy()
+    return (indptr, indices, data), x.cpu().numpy()
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU path (torch.spmm, all host threads) on the same
+    config; each step is a bounded sample (a slab of rows of one hop)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import sgc_b200
+    name = args.workload
+    threads = os.cpu_count() or 1
+    if torch.cuda.is_available():
+        dev = torch.device("cuda", 0)
+        s = make_workload(name, dev)
+        graph = sgc_b200.normalize_csr(s["n"], s["row_ptr"], s["col"], s["val"])
+        csr, x_host = host_copies(graph, s["x"])
+        n, f, k, nnz = s["n"], s["f"], s["k"], graph.nnz
+        del graph, s
+        torch.cuda.empty_cache()
+    else:  # no GPU: build S with the reference's own host code
+        from oracle import reference_port as rp
+        import scipy.sparse as sp
+        s = make_workload(name, "cpu")
+        a = sp.csr_matrix((s["val"].numpy(), s["col"].numpy(), s["row_ptr"].numpy()), shape=(s["n"], s["n"]))
+        S = rp.aug_normalized_adjacency(a).tocsr()
+        S.sort_indices()
+        csr = (S.indptr.astype(np.int64), S.indices.astype(np.int32), S.data.astype(np.float32))
+        x_host = s["x"].numpy()
+        n, f, k, nnz = s["n"], s["f"], s["k"], S.nnz
+    from oracle import reference_port as rp
+    import scipy.sparse as sp
+    rows = max(1, n // env_int("SGC_BENCH_CPU_FRACTION", 16))
+    torch.set_num_threads(threads)
+    indptr, indices, data = csr
+    sub = sp.csr_matrix((data[:indptr[rows]], indices[:indptr[rows]], indptr[:rows + 1]), shape=(rows, n))
+    adj = rp.sparse_mx_to_torch_sparse_tensor(sub)
+    x = torch.from_numpy(x_host)
+    if name == "reddit":
+        x = rp.standardize(x)
+    for _ in range(args.warmup):
+        rp.sgc_precompute(x, adj, 1)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        rp.sgc_precompute(x, adj, 1)
+    secs = (time.perf_counter() - t0) / args.steps
+    sample_nnz = int(indptr[rows])
+    value = sample_nnz * f / secs
+    sample = "rows [0,%d) of one hop (%d of %d stored entries), torch.spmm fp32" % (rows, sample_nnz, nnz)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": secs * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(name, n, nnz, f, k),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def workload_config(name, n, nnz, f, k, **extra):
+    label = {"reddit": "Reddit-shaped synthetic inductive SGC K=2 (BASELINE configs[2])",
+             "products": "ogbn-products-shaped synthetic power-law graph K=3 (BASELINE configs[3])",
+             "papers100m": "ogbn-papers100M-shaped synthetic K=3 (BASELINE configs[4])"}[name]
+    cfg = {"workload": label, "nodes": n, "nnz_S": nnz, "features": f, "k_hops": k,
+           "l2_hygiene": "inputs larger than L2 (X %.0f MB + CSR %.0f MB vs 126 MB L2); no flush"
+                         % (n * f * 4 / 1e6, nnz * 12 / 1e6)}
+    cfg.update(extra)
+    return cfg
+
+
+def run_own(args):
+    import torch.distributed as dist
+    import sgc_b200
+    from sgc_b200 import _ffi
+    from sgc_b200.features import StandardizedFeatures
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    if world > 1:
+        from sgc_b200 import dist as sgc_dist
+        return sgc_dist.bench(args, rank, world, dev, globals())
+
+    name = args.workload
+    s = make_workload(name, dev)
+    n, f, k = s["n"], s["f"], s["k"]
+    torch.cuda.synchronize()
+    # ---- one-off preparation, timed separately (K1 + K2, K3) ----
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+    e0, e1, e2 = ev(), ev(), ev()
+    e0.record()
+    graph = sgc_b200.normalize_csr(n, s["row_ptr"], s["col"], s["val"])
+    e1.record()
+    feats = s["x"]
+    if name == "reddit":
+        mean, std = sgc_b200.col_stats(feats)
+        feats = StandardizedFeatures(feats, mean, std)
+    e2.record()
+    torch.cuda.synchronize()
+    normalise_ms, stats_ms = e0.elapsed_time(e1), e1.elapsed_time(e2)
+    nnz = graph.nnz
+    graph.plan(sgc_b200.propagate.default_chunk())
+
+    raw = feats.unwrap() if isinstance(feats, StandardizedFeatures) else (feats, None, None)
+
+    def step():
+        return sgc_b200.propagate(graph, raw[0], k, mean=raw[1], std=raw[2])
+
+    for _ in range(args.warmup):
+        y = step()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local)
+    sampler.start()
+    launches0 = _ffi.launch_count()
+    start, stop = ev(), ev()
+    start.record()
+    for _ in range(args.steps):
+        y = step()
+    stop.record()
+    torch.cuda.synchronize()
+    launches = _ffi.launch_count() - launches0
+    total_ms = start.elapsed_time(stop)
+    clocks = sampler.stop()
+    ms_per_step = total_ms / args.steps
+    value = k * nnz * f / (ms_per_step * 1e-3)
+
+    # ---- per-hop kernel time (CUDA events on the launching stream) ----
+    hop_ms = []
+    mean32, std32 = raw[1], raw[2]
+    ybuf = torch.empty((n, f), dtype=torch.float32, device=dev)
+    ybuf2 = torch.empty((n, f), dtype=torch.float32, device=dev)
+    for hop_id in range(2):
+        ts = []
+        for _ in range(max(3, min(args.steps, 10))):
+            a, b = ev(), ev()
+            a.record()
+            if hop_id == 0:
+                sgc_b200.hop(graph, raw[0], mean=mean32, std=std32, out=ybuf)
+            else:
+                sgc_b200.hop(graph, ybuf, out=ybuf2)
+            b.record()
+            torch.cuda.synchronize()
+            ts.append(a.elapsed_time(b))
+        hop_ms.append(float(np.median(ts)))
+    peak, peak_src = peaks()
+    b_hop = hop_bytes(n, nnz, f)
+    avg_launch_s = ms_per_step * 1e-3 / k
+    achieved = b_hop / avg_launch_s / 1e9
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": ncu_traffic(name), "peak_source": peak_src, "kernel": "spmm_hop_kernel",
+                "algorithmic_bytes_per_launch": b_hop,
+                "compulsory_bytes_per_launch": 12 * nnz + 8 * (n + 1) + 8 * f * n,
+                "hop_ms": hop_ms}
+
+    # ---- end to end through the public API with HOST buffers ----
+    e2e = None if args.skip_e2e else run_e2e(args, s, name, k, nnz, dev)
+
+    # ---- the reference's CPU path on this box's host cores (bounded sample) ----
+    cpu = None
+    if not args.no_cpu_baseline:
+        csr, x_host = host_copies(graph, s["x"])
+        threads = os.cpu_count() or 1
+        rows = max(1, n // env_int("SGC_BENCH_CPU_FRACTION", 8))
+        m = mean32.cpu().numpy() if mean32 is not None else None
+        sd = std32.cpu().numpy() if std32 is not None else None
+        rate, secs, sample_nnz = cpu_reference_rate(csr, x_host, m, sd, rows, 3, threads)
+        cpu = {"value": rate, "unit": UNIT, "cores": threads, "kind": "port",
+               "sample": "rows [0,%d) of one hop (%d of %d stored entries), torch.spmm fp32 on CPU, median of 3 (%.2f s each)"
+                         % (rows, sample_nnz, nnz, secs)}
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(name, n, nnz, f, k, normalise_ms=normalise_ms, col_stats_ms=stats_ms,
+                                  chunk=sgc_b200.propagate.default_chunk(),
+                                  fused=["D^-1/2 scaling", "feature standardisation (hop 1)"] if name == "reddit"
+                                  else ["D^-1/2 scaling"]),
+        "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+    }
+    print(json.dumps(line))
+
+
+def run_e2e(args, s, name, k, nnz_s, dev):
+    """Same metric through the reference-facing API with host buffers: every step uploads the raw
+    adjacency (CSR of A) and the raw features from pinned host memory, normalises on the GPU
+    (K1+K2), computes the column statistics (K3), runs the K hops and reads the propagated
+    features back to pinned host memory."""
+    import sgc_b200
+    from sgc_b200.features import StandardizedFeatures
+    n, f = s["n"], s["f"]
+    host = {kk: s[kk].cpu().pin_memory() for kk in ("row_ptr", "col", "val", "x")}
+    out_host = torch.empty((n, f), dtype=torch.float32).pin_memory()
+    h2d = sum(t.numel() * t.element_size() for t in host.values())
+    d2h = out_host.numel() * 4
+
+    def step():
+        rp = host["row_ptr"].to(dev, non_blocking=True)
+        col = host["col"].to(dev, non_blocking=True)
+        val = host["val"].to(dev, non_blocking=True)
+        x = host["x"].to(dev, non_blocking=True)
+        graph = sgc_b200.normalize_csr(n, rp, col, val)
+        feats = x
+        if name == "reddit":
+            mean, std = sgc_b200.col_stats(x)
+            feats = StandardizedFeatures(x, mean, std)
+        y, _ = sgc_b200.sgc_precompute(feats, graph, k)
+        out_host.copy_(y, non_blocking=True)
+        torch.cuda.synchronize()
+
+    steps = max(2, min(args.steps, 5))
+    step()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    secs = (time.perf_counter() - t0) / steps
+    return {"value": k * nnz_s * f / secs, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+            "d2h_bytes_per_step": int(d2h), "ms_per_step": secs * 1e3, "steps": steps,
+            "path": "host CSR(A)+X -> H2D -> aug_normalized_adjacency (K1,K2) -> col_stats (K3) -> sgc_precompute -> D2H"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="own", choices=["own", "reference"])
+    ap.add_argument("--workload", default=None, choices=[None, "reddit", "products", "papers100m"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--skip-e2e", action="store_true", help="profiling runs only: leaves e2e null")
+    args = ap.parse_args()
+    if args.workload is None:
+        args.workload = "reddit"
+    args.warmup = max(args.warmup, 3) if args.impl == "own" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_own(args)
+
+
+if __name__ == "__main__":
+    main()
