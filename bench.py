@@ -255,7 +255,7 @@ def run_own(args):
     raw = feats.unwrap() if isinstance(feats, StandardizedFeatures) else (feats, None, None)
 
     def step():
-        return sgc_b200.propagate(graph, raw[0], k, mean=raw[1], std=raw[2])
+        return sgc_b200.propagate.propagate(graph, raw[0], k, mean=raw[1], std=raw[2])
 
     for _ in range(args.warmup):
         y = step()

@@ -56,8 +56,10 @@ def test_normalisation_matches_reference(dev, ds):
     assert np.array_equal(coo_rows(graph), g["S_row"])                       # row_ptr bit-exact
     assert np.array_equal(graph.col.cpu().numpy().astype(np.int64), g["S_col"])   # col_idx bit-exact
     s64 = graph.values64().cpu().numpy()
-    # fp64 values: the reference's own pow() is host-dependent in the last bit (glibc vs SVML)
-    assert ulp64(s64, g["S_data64"]) <= 2
+    # fp64 values: d_i and d_j are each within 1 ulp of numpy's pow() (itself host-dependent in the
+    # last bit: glibc vs SVML), so the product (d_i*a)*d_j is within a few ulp(fp64); the fp32
+    # rounding the reference feeds to torch.spmm is compared bit for bit below
+    assert ulp64(s64, g["S_data64"]) <= 4
     if "S_val32_sha" in g.files:
         assert sha(graph.values32().cpu().numpy()) == str(g["S_val32_sha"])   # the fp32 S the reference feeds torch.spmm
         idx = graph.coo_indices().cpu().numpy()
@@ -87,7 +89,7 @@ def test_normalisation_edge_cases(dev):
         if name == "non_canonical":
             assert np.allclose(got[ok], ref[ok], rtol=1e-15, atol=0), name
         else:
-            assert ulp64(got[ok], ref[ok]) <= 2, name
+            assert ulp64(got[ok], ref[ok]) <= 4, name
 
 
 def test_scipy_entry_point(dev):
@@ -102,7 +104,7 @@ def test_scipy_entry_point(dev):
     coo = S.tocoo()
     assert sp.isspmatrix_coo(coo) and coo.dtype == np.float64
     assert np.array_equal(coo.row, g["S_row"]) and np.array_equal(coo.col, g["S_col"])
-    assert ulp64(coo.data, g["S_data64"]) <= 2
+    assert ulp64(coo.data, g["S_data64"]) <= 4
     import utils as drop_utils
     t = drop_utils.sparse_mx_to_torch_sparse_tensor(S)
     assert t.is_sparse and t.dtype == torch.float32 and t._indices().dtype == torch.int64
