@@ -219,8 +219,6 @@ def run_own(args):
     import torch.distributed as dist
     import sgc_b200
     from sgc_b200 import _ffi
-    from sgc_b200.features import StandardizedFeatures
-
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -238,24 +236,31 @@ def run_own(args):
     torch.cuda.synchronize()
     # ---- one-off preparation, timed separately (K1 + K2, K3) ----
     ev = lambda: torch.cuda.Event(enable_timing=True)
-    e0, e1, e2 = ev(), ev(), ev()
-    e0.record()
-    graph = sgc_b200.normalize_csr(n, s["row_ptr"], s["col"], s["val"])
-    e1.record()
-    feats = s["x"]
+    def timed(fn):
+        a, b = ev(), ev()
+        torch.cuda.synchronize()
+        a.record()
+        out = fn()
+        b.record()
+        torch.cuda.synchronize()
+        return out, a.elapsed_time(b)
+
+    graph, normalise_ms = timed(lambda: sgc_b200.normalize_csr(n, s["row_ptr"], s["col"], s["val"]))
+    # features in the layout the loaders produce (utils.load_reddit_data): padded row stride
+    x = sgc_b200.to_padded(s["x"])
+    mean32 = std32 = x_raw = None
+    stats_ms = standardise_ms = 0.0
     if name == "reddit":
-        mean, std = sgc_b200.col_stats(feats)
-        feats = StandardizedFeatures(feats, mean, std)
-    e2.record()
-    torch.cuda.synchronize()
-    normalise_ms, stats_ms = e0.elapsed_time(e1), e1.elapsed_time(e2)
+        (mean32, std32), stats_ms = timed(lambda: sgc_b200.col_stats(x))
+        x_raw = sgc_b200.features.padded_rows(n, f, dev)   # raw copy kept for the fused-hop variants below
+        x_raw.copy_(x)
+        _, standardise_ms = timed(lambda: sgc_b200.standardize_(x, mean32, std32))   # utils.py:119, exact, in place
     nnz = graph.nnz
     graph.plan(sgc_b200.propagate.default_chunk())
 
-    raw = feats.unwrap() if isinstance(feats, StandardizedFeatures) else (feats, None, None)
-
     def step():
-        return sgc_b200.propagate.propagate(graph, raw[0], k, mean=raw[1], std=raw[2])
+        # what utils.sgc_precompute times in the reference: K hops on (standardised) features
+        return sgc_b200.propagate.propagate(graph, x, k)
 
     for _ in range(args.warmup):
         y = step()
@@ -276,23 +281,24 @@ def run_own(args):
     value = k * nnz * f / (ms_per_step * 1e-3)
 
     # ---- per-hop kernel time (CUDA events on the launching stream) ----
-    hop_ms = []
-    mean32, std32 = raw[1], raw[2]
-    ybuf = torch.empty((n, f), dtype=torch.float32, device=dev)
-    ybuf2 = torch.empty((n, f), dtype=torch.float32, device=dev)
-    for hop_id in range(2):
+    def hop_time(fn):
         ts = []
         for _ in range(max(3, min(args.steps, 10))):
             a, b = ev(), ev()
             a.record()
-            if hop_id == 0:
-                sgc_b200.hop(graph, raw[0], mean=mean32, std=std32, out=ybuf)
-            else:
-                sgc_b200.hop(graph, ybuf, out=ybuf2)
+            fn()
             b.record()
             torch.cuda.synchronize()
             ts.append(a.elapsed_time(b))
-        hop_ms.append(float(np.median(ts)))
+        return float(np.median(ts))
+
+    ybuf = sgc_b200.features.padded_rows(n, f, dev)
+    hop_ms = {"plain": hop_time(lambda: sgc_b200.hop(graph, x, out=ybuf))}
+    if name == "reddit":
+        for mode in ("rcp", "div"):
+            hop_ms["fused_std_" + mode] = hop_time(
+                lambda: sgc_b200.hop(graph, x_raw, mean=mean32, std=std32, std_mode=mode, out=ybuf))
+    del x_raw
     peak, peak_src = peaks()
     b_hop = hop_bytes(n, nnz, f)
     avg_launch_s = ms_per_step * 1e-3 / k
@@ -309,12 +315,10 @@ def run_own(args):
     # ---- the reference's CPU path on this box's host cores (bounded sample) ----
     cpu = None
     if not args.no_cpu_baseline:
-        csr, x_host = host_copies(graph, s["x"])
+        csr, x_host = host_copies(graph, x)
         threads = os.cpu_count() or 1
         rows = max(1, n // env_int("SGC_BENCH_CPU_FRACTION", 8))
-        m = mean32.cpu().numpy() if mean32 is not None else None
-        sd = std32.cpu().numpy() if std32 is not None else None
-        rate, secs, sample_nnz = cpu_reference_rate(csr, x_host, m, sd, rows, 3, threads)
+        rate, secs, sample_nnz = cpu_reference_rate(csr, x_host, None, None, rows, 3, threads)
         cpu = {"value": rate, "unit": UNIT, "cores": threads, "kind": "port",
                "sample": "rows [0,%d) of one hop (%d of %d stored entries), torch.spmm fp32 on CPU, median of 3 (%.2f s each)"
                          % (rows, sample_nnz, nnz, secs)}
@@ -324,9 +328,12 @@ def run_own(args):
         "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": workload_config(name, n, nnz, f, k, normalise_ms=normalise_ms, col_stats_ms=stats_ms,
+                                  standardise_inplace_ms=standardise_ms,
                                   chunk=sgc_b200.propagate.default_chunk(),
-                                  fused=["D^-1/2 scaling", "feature standardisation (hop 1)"] if name == "reddit"
-                                  else ["D^-1/2 scaling"]),
+                                  fused_into_hop=["D^-1/2 row/column scaling (S never materialised)"],
+                                  timed_region="K hops on device-resident CSR + standardised X, as "
+                                               "utils.py:93-96 times them; K1/K2/K3 + standardisation "
+                                               "timed separately (above) and inside e2e"),
         "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
     }
     print(json.dumps(line))
@@ -349,7 +356,7 @@ def run_e2e(args, s, name, k, nnz_s, dev):
         rp = host["row_ptr"].to(dev, non_blocking=True)
         col = host["col"].to(dev, non_blocking=True)
         val = host["val"].to(dev, non_blocking=True)
-        x = host["x"].to(dev, non_blocking=True)
+        x = sgc_b200.to_padded(host["x"], dev)          # H2D straight into padded device rows
         graph = sgc_b200.normalize_csr(n, rp, col, val)
         feats = x
         if name == "reddit":

@@ -119,6 +119,11 @@ int32_t sgc_col_stats(const float *x_d, int64_t n, int64_t f, int64_t ld, float 
                       float *std32_d, double *mean64_d, double *std64_d, void *ws_d,
                       size_t ws_bytes, void *stream);
 
+/* x <- (x - mean[c]) / std[c] in place, the fp32 expression of utils.py:119 evaluated exactly
+ * (one subtraction, one IEEE division per element).  x_d: fp32 [n, ld] row-major. */
+int32_t sgc_standardize_inplace(float *x_d, int64_t n, int64_t f, int64_t ld, const float *mean_d,
+                                const float *std_d, void *stream);
+
 /* ---- K4: load-balanced CSR SpMM hop             (utils.py:95, torch.spmm) ------------------ */
 typedef struct sgc_plan sgc_plan_t;
 

@@ -1,5 +1,5 @@
-"""Feature-side pieces of the path: column statistics (K3) and the lazily standardised feature
-matrix that lets the first propagation hop apply ``(x - mean) / std`` in registers.
+"""Feature-side pieces of the path: column statistics (K3), the exact in-place standardisation
+pass, padded feature storage, and the lazily standardised feature matrix.
 
 Reference behaviour being replaced: /root/reference/utils.py:118-119
     features = torch.FloatTensor(np.array(features))
@@ -7,8 +7,9 @@ Reference behaviour being replaced: /root/reference/utils.py:118-119
 which materialises a standardised copy on the CPU.  Here `load_reddit_data` returns a
 `StandardizedFeatures`: the raw fp32 matrix in HBM plus fp32 mean/std vectors.  It behaves like the
 standardised tensor for every consumer (any torch op on it sees ``(raw-mean)/std``), row selection
-(``features[idx_train]``, reddit.py:45) stays lazy, and ``sgc_precompute`` hands raw + statistics
-to the fused first hop.
+(``features[idx_train]``, reddit.py:45) stays lazy, and ``sgc_precompute`` either standardises the
+storage in place with one exact streaming pass before the first hop (default) or hands raw +
+statistics to the first hop, which then standardises the gathered values in registers.
 """
 import torch
 
@@ -37,6 +38,40 @@ def col_stats(x, want64=False):
     return (mean32, std32, mean64, std64) if want64 else (mean32, std32)
 
 
+def padded_rows(n, f, device):
+    """fp32 [n, f] view whose rows start 32 bytes apart-aligned: leading dimension rounded up to a
+    multiple of 8 floats (602 -> 608), pad columns zero.  Gathers of such rows are whole 16-byte
+    vectors, which is what the propagation kernel's fast path needs."""
+    ld = (f + 7) // 8 * 8
+    base = torch.empty((n, ld), dtype=torch.float32, device=device)
+    if ld != f:
+        base[:, f:].zero_()
+    return base[:, :f]
+
+
+def to_padded(x, device=None):
+    """Copy (host or device) features into padded device storage; no-op if already laid out so."""
+    device = x.device if device is None else device
+    n, f = x.shape
+    if x.device == torch.device(device) and x.dtype == torch.float32 and x.stride(1) == 1 \
+            and x.stride(0) % 4 == 0 and x.data_ptr() % 16 == 0:
+        return x
+    out = padded_rows(n, f, device)
+    out.copy_(x, non_blocking=True)
+    return out
+
+
+def standardize_(x, mean, std):
+    """In place x <- (x - mean) / std (utils.py:119), exact fp32 expression, on the GPU."""
+    dev = require_cuda(x.device)
+    if x.dtype != torch.float32 or x.dim() != 2 or x.stride(1) != 1:
+        raise TypeError("standardize_ expects a 2-D float32 tensor with unit column stride")
+    with torch.cuda.device(dev):
+        _ffi.call("sgc_standardize_inplace", x.data_ptr(), x.shape[0], x.shape[1], x.stride(0),
+                  _ffi.ptr(mean), _ffi.ptr(std), stream_ptr())
+    return x
+
+
 def _getter(name):
     return getattr(torch.Tensor, name).__get__
 
@@ -58,12 +93,24 @@ class StandardizedFeatures(torch.Tensor):
     @staticmethod
     def __new__(cls, raw, mean, std):
         t = torch.Tensor._make_subclass(cls, raw.detach(), False)
-        t._sgc_mean, t._sgc_std = mean, std
+        t._sgc_mean, t._sgc_std, t._sgc_applied = mean, std, False
         return t
 
     def unwrap(self):
+        """(storage, mean, std); mean/std are None once the storage holds standardised values."""
         with torch._C.DisableTorchFunctionSubclass():
-            return self.as_subclass(torch.Tensor), self._sgc_mean, self._sgc_std
+            raw = self.as_subclass(torch.Tensor)
+        if self._sgc_applied:
+            return raw, None, None
+        return raw, self._sgc_mean, self._sgc_std
+
+    def apply_(self):
+        """Standardise the storage in place (one streaming pass, 8 B/element) and remember it."""
+        if not self._sgc_applied:
+            raw, mean, std = self.unwrap()
+            standardize_(raw, mean, std)
+            self._sgc_applied = True
+        return self
 
     @staticmethod
     def materialize(raw, mean, std):
@@ -72,7 +119,7 @@ class StandardizedFeatures(torch.Tensor):
 
     def standardized(self):
         raw, mean, std = self.unwrap()
-        return StandardizedFeatures.materialize(raw, mean, std)
+        return raw if mean is None else StandardizedFeatures.materialize(raw, mean, std)
 
     @classmethod
     def __torch_function__(cls, func, types, args=(), kwargs=None):
@@ -90,7 +137,11 @@ class StandardizedFeatures(torch.Tensor):
             if not isinstance(idx, (torch.Tensor, slice, int)):
                 idx = torch.as_tensor(idx, device=raw.device)
             rows = raw[idx]
-            return StandardizedFeatures(rows, mean, std) if rows.dim() == 2 else (rows - mean) / std
+            if mean is None:
+                return rows
+            if rows.dim() != 2:
+                return (rows - mean) / std
+            return StandardizedFeatures(to_padded(rows) if rows.is_cuda else rows, mean, std)
         # anything else sees the standardised values
         conv = lambda a: a.standardized() if isinstance(a, StandardizedFeatures) else a
         args = tuple(conv(a) for a in args)

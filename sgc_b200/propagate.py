@@ -34,8 +34,14 @@ def default_slab():
 
 
 def default_std_mode():
-    """'div' reproduces utils.py:119 exactly ((x-mean)/std); 'rcp' multiplies by 1/std."""
-    return _ENV("SGC_B200_STD", "div")
+    """How `sgc_precompute` applies the Reddit feature standardisation (utils.py:119) to a
+    `StandardizedFeatures` input (SGC_B200_STD):
+      'inplace' (default) one streaming pass standardises the feature storage in place, exactly,
+                before the first hop (0.2 ms at the Reddit shape);
+      'div' / 'rcp'       fused into the first hop's gather: exact division, or multiplication by
+                1/std (<= 1 ulp per element).  Measured on B200 the gather touches every row of X
+                ~100 times, so per-element work inside it costs 3-13 ms -- see DESIGN.md."""
+    return _ENV("SGC_B200_STD", "inplace")
 
 
 def _pad8(f):
@@ -66,7 +72,7 @@ def _hop_args(g, plan, x, ldx, y, ldy, f, partial, mean, std, std_mode, slab, hi
     else:
         a.sval_d = _ffi.ptr(g.sval)
     if mean is not None:
-        flags |= _ffi.HOP_STD_DIV if std_mode == "div" else _ffi.HOP_STD_RCP
+        flags |= _ffi.HOP_STD_RCP if std_mode == "rcp" else _ffi.HOP_STD_DIV
         a.mean_d, a.std_d = _ffi.ptr(mean), _ffi.ptr(std)
     a.x_d, a.ldx, a.y_d, a.ldy = x, ldx, y, ldy
     if partial is not None:
@@ -160,11 +166,14 @@ def sgc_precompute(features, adj, degree, **kw):
     if int(degree) <= 0:
         return features, 0.0            # utils.py:94: the loop does not run; same object back
     mean = std = None
-    if isinstance(features, StandardizedFeatures):
-        features, mean, std = features.unwrap()
     g = as_graph(adj)
     torch.cuda.synchronize(g.device)
     t = perf_counter()
+    if isinstance(features, StandardizedFeatures):
+        if (kw.get("std_mode") or default_std_mode()) == "inplace":
+            features.apply_()
+            kw.pop("std_mode", None)
+        features, mean, std = features.unwrap()
     out = propagate(g, features, degree, mean=mean, std=std, **kw)
     torch.cuda.synchronize(g.device)
     return out, perf_counter() - t

@@ -22,7 +22,7 @@ import scipy.sparse as sp
 import torch
 
 from . import _ffi
-from .features import StandardizedFeatures, col_stats
+from .features import StandardizedFeatures, col_stats, to_padded
 from .graph import SgcGraph, require_cuda
 from .normalization import fetch_normalization, row_normalize
 from .propagate import sgc_precompute  # noqa: F401  (re-exported: the reference's utils.sgc_precompute)
@@ -109,7 +109,8 @@ def load_citation(dataset_str="cora", normalization="AugNormAdj", cuda=True):
     adj, features = preprocess_citation(adj, features, normalization)   # adjacency: GPU kernels
 
     n_train = len(parts["y"])
-    features = torch.from_numpy(np.asarray(features.todense(), dtype=np.float32)).to(dev)
+    # dense fp32 features in padded device storage (row stride a multiple of 8 floats)
+    features = to_padded(torch.from_numpy(np.asarray(features.todense(), dtype=np.float32)), dev)
     labels = torch.from_numpy(labels).long().max(dim=1)[1].to(dev)
     idx_train = torch.arange(n_train, dtype=torch.long, device=dev)
     idx_val = torch.arange(n_train, n_train + 500, dtype=torch.long, device=dev)
@@ -140,7 +141,7 @@ def load_reddit_data(data_path="data/", normalization="AugNormAdj", cuda=True):
     labels[test_index] = y_test
     adj = adj + adj.T                                           # utils.py:116
     train_adj = adj[train_index, :][:, train_index]             # utils.py:117
-    raw = torch.from_numpy(np.ascontiguousarray(feats, dtype=np.float32)).to(dev)
+    raw = to_padded(torch.from_numpy(np.ascontiguousarray(feats, dtype=np.float32)), dev)
     mean, std = col_stats(raw)                                  # utils.py:119 statistics (K3)
     features = StandardizedFeatures(raw, mean, std)             # standardisation fused into hop 1
     normalizer = fetch_normalization(normalization)

@@ -229,14 +229,24 @@ def test_fused_standardisation(dev):
     assert np.array_equal(got.cpu().numpy(), want)
     got_rcp = sgc_b200.hop(graph, x, mean=mean32, std=std32, chunk=0, std_mode="rcp")
     assert np.allclose(got_rcp.cpu().numpy(), want, rtol=RTOL, atol=ATOL)
-    # through the public API: StandardizedFeatures in, two hops out
-    feats = sgc_b200.StandardizedFeatures(x, mean32, std32)
-    y, _ = sgc_b200.sgc_precompute(feats, graph, 2, chunk=0)
+    # through the public API: StandardizedFeatures in, two hops out -- fused and in-place modes
     want2 = so.spmm_hop(rp, col, val, want)
+    feats = sgc_b200.StandardizedFeatures(x.clone(), mean32, std32)
+    y, _ = sgc_b200.sgc_precompute(feats, graph, 2, chunk=0, std_mode="div")
     assert np.array_equal(y.cpu().numpy(), want2)
-    sub = feats[np.arange(0, 50)]
+    sub = feats[np.arange(0, 50)]                     # reddit.py:45 indexes with an ndarray
     assert isinstance(sub, sgc_b200.StandardizedFeatures)
     assert torch.equal(sub.standardized(), ((x - mean32) / std32)[:50])
+    assert sub.unwrap()[0].stride(0) % 8 == 0          # re-padded for the aligned gather path
+    # default mode: one exact in-place pass over the feature storage, then plain hops
+    feats2 = sgc_b200.StandardizedFeatures(sgc_b200.to_padded(x.clone()), mean32, std32)
+    y2, _ = sgc_b200.sgc_precompute(feats2, graph, 2, chunk=0)
+    assert np.array_equal(y2.cpu().numpy(), want2)
+    raw2, m2, s2 = feats2.unwrap()
+    assert m2 is None and torch.equal(raw2, (x - mean32) / std32)      # storage now holds utils.py:119's values
+    assert torch.equal(feats2[np.arange(0, 50)], ((x - mean32) / std32)[:50])
+    y3, _ = sgc_b200.sgc_precompute(feats2, graph, 2, chunk=0)         # idempotent: not applied twice
+    assert torch.equal(y3, y2)
 
 
 def test_downstream_accuracy_unchanged(dev):
@@ -309,6 +319,8 @@ def test_full_size_reddit_shape_properties(dev):
     want2 = so.spmm_hop(sub_ptr, col[take], val[take], y1.cpu().numpy())
     assert np.allclose(y2.cpu().numpy()[pick], want2, rtol=RTOL, atol=ATOL)
     # (4) the K-hop entry point agrees with hop-by-hop
-    feats = sgc_b200.StandardizedFeatures(x, mean, std)
-    yk, secs = sgc_b200.sgc_precompute(feats, graph, 2)
+    feats = sgc_b200.StandardizedFeatures(sgc_b200.to_padded(x.clone()), mean, std)
+    yk, secs = sgc_b200.sgc_precompute(feats, graph, 2, std_mode="div")
     assert torch.equal(yk, y2) and secs > 0
+    yi, _ = sgc_b200.sgc_precompute(feats, graph, 2)                    # in-place standardisation (default)
+    assert torch.equal(yi, y2)
