@@ -387,6 +387,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--skip-e2e", action="store_true", help="profiling runs only: leaves e2e null")
     args = ap.parse_args()
+    args.workload_given = args.workload is not None
     if args.workload is None:
         args.workload = "reddit"
     args.warmup = max(args.warmup, 3) if args.impl == "own" else args.warmup

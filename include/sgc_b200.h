@@ -70,14 +70,17 @@ int32_t sgc_csr_canonicalize(int64_t n_rows, int64_t nnz, const int64_t *row_ptr
                              void *stream);
 /* Pass 1: per-row entry count of A+I (existing diagonal merged, results that are exactly zero
  * dropped, as scipy's csr_plus_csr does), exclusive-scanned into row_ptr_out_d[n+1]. Input must
- * be canonical. */
-int32_t sgc_csr_selfloop_count(int64_t n, const int64_t *row_ptr_d, const int32_t *col_d,
-                               const double *val_d, int64_t *row_ptr_out_d, void *ws_d,
-                               size_t ws_bytes, void *stream);
+ * be canonical.  The n rows may be a slice [diag_offset, diag_offset+n) of a larger square
+ * matrix with global column ids (row-sharded multi-GPU): row i's diagonal is column
+ * diag_offset+i.  diag_offset = 0 for a whole matrix. */
+int32_t sgc_csr_selfloop_count(int64_t n, int64_t diag_offset, const int64_t *row_ptr_d,
+                               const int32_t *col_d, const double *val_d, int64_t *row_ptr_out_d,
+                               void *ws_d, size_t ws_bytes, void *stream);
 /* Pass 2: sorted merge-insert of (i,i); writes col_out_d / aval_out_d (fp64 values of A+I). */
-int32_t sgc_csr_selfloop_build(int64_t n, const int64_t *row_ptr_d, const int32_t *col_d,
-                               const double *val_d, const int64_t *row_ptr_out_d,
-                               int32_t *col_out_d, double *aval_out_d, void *stream);
+int32_t sgc_csr_selfloop_build(int64_t n, int64_t diag_offset, const int64_t *row_ptr_d,
+                               const int32_t *col_d, const double *val_d,
+                               const int64_t *row_ptr_out_d, int32_t *col_out_d,
+                               double *aval_out_d, void *stream);
 
 /* ---- K2: degree reduction and D^-1/2            (normalization.py:8-10) ------------------- */
 /* rowsum_d[i] = sum of row i of A+I accumulated in stored order in fp64; dinv_d[i] =
@@ -89,18 +92,21 @@ int32_t sgc_degree_inv_sqrt(int64_t n, const int64_t *row_ptr_d, const double *a
 /* ---- S = D^-1/2 (A+I) D^-1/2 structure + values (normalization.py:11-12, utils.py:25) ------ */
 /* scipy's two CSR products drop entries whose product is exactly zero (rows/columns with
  * d == 0).  count: per-row kept entries, scanned into row_ptr_out_d[n+1]; also writes the number
- * of dropped entries to dropped_d[0] (when 0 the input structure can be reused as is). */
+ * of dropped entries to dropped_d[0] (when 0 the input structure can be reused as is).
+ * dinv_rows_d[i] is D^-1/2 of row i, dinv_d[c] of column c (the same array for a whole square
+ * matrix; dinv_d + row_begin for a row slice). */
 int32_t sgc_norm_count(int64_t n, const int64_t *row_ptr_d, const int32_t *col_d,
-                       const double *aval_d, const double *dinv_d, int64_t *row_ptr_out_d,
-                       int64_t *dropped_d, void *ws_d, size_t ws_bytes, void *stream);
+                       const double *aval_d, const double *dinv_rows_d, const double *dinv_d,
+                       int64_t *row_ptr_out_d, int64_t *dropped_d, void *ws_d, size_t ws_bytes,
+                       void *stream);
 /* build: compacts (col, aval) to the kept entries and optionally materialises the normalised
  * values: s64_out_d = (d_i*a_ij)*d_j in fp64 (what normalization.py:12 returns) and s32_out_d =
  * the same rounded once to fp32 (utils.py:25).  Any of col_out_d/aval_out_d/s64_out_d/s32_out_d
  * may be NULL.  row_ptr_out_d == row_ptr_d means "structure unchanged". */
 int32_t sgc_norm_build(int64_t n, const int64_t *row_ptr_d, const int32_t *col_d,
-                       const double *aval_d, const double *dinv_d, const int64_t *row_ptr_out_d,
-                       int32_t *col_out_d, double *aval_out_d, double *s64_out_d,
-                       float *s32_out_d, void *stream);
+                       const double *aval_d, const double *dinv_rows_d, const double *dinv_d,
+                       const int64_t *row_ptr_out_d, int32_t *col_out_d, double *aval_out_d,
+                       double *s64_out_d, float *s32_out_d, void *stream);
 /* CSR row pointers -> COO row indices (int64), and int32 -> int64 columns: the [2, nnz] index
  * tensor of utils.py:26-27.  idx_out_d has 2*nnz int64 (rows then cols). */
 int32_t sgc_csr_to_coo(int64_t n, const int64_t *row_ptr_d, const int32_t *col_d, int64_t nnz,
@@ -149,7 +155,8 @@ int64_t sgc_spmm_plan_partial_rows(const sgc_plan_t *plan);
 
 typedef struct sgc_hop_args {
     const double *aval_d;      /* FUSED_NORM: fp64 values of A+I (pruned structure)          */
-    const double *dinv_d;      /* FUSED_NORM: D^-1/2, n_cols entries                          */
+    const double *dinv_d;      /* FUSED_NORM: D^-1/2 by column, n_cols entries                */
+    const double *dinv_rows_d; /* FUSED_NORM: D^-1/2 by row, n_rows entries; NULL = dinv_d    */
     const float  *sval_d;      /* !FUSED_NORM: fp32 values of S                               */
     const float  *x_d;         /* gathered operand [n_cols, ldx] fp32                         */
     int64_t       ldx;

@@ -2,7 +2,8 @@
 ``normalization.aug_normalized_adjacency`` and ``utils.sgc_precompute`` of bellaj09/SGC, behind the
 reference's own Python API.  CUDA kernels live in sgc_b200/csrc (C ABI: include/sgc_b200.h);
 PyTorch is used for device memory, streams and torch.distributed only."""
-from .graph import SgcGraph, from_scipy, from_torch_sparse, normalize_csr  # noqa: F401
+from .graph import (SgcGraph, augment_csr, finish_normalization, from_scipy, from_torch_sparse,  # noqa: F401
+                    normalize_csr)
 from .features import StandardizedFeatures, col_stats, standardize_, to_padded  # noqa: F401
 from . import propagate  # noqa: F401  (module: propagate.propagate() is the stream-ordered K-hop call)
 from .propagate import hop, sgc_precompute  # noqa: F401

@@ -21,7 +21,7 @@ HOP_STD_RCP = 4
 class HopArgs(ctypes.Structure):
     """struct sgc_hop_args (include/sgc_b200.h)."""
     _fields_ = [
-        ("aval_d", c_p), ("dinv_d", c_p), ("sval_d", c_p),
+        ("aval_d", c_p), ("dinv_d", c_p), ("dinv_rows_d", c_p), ("sval_d", c_p),
         ("x_d", c_p), ("ldx", c_i64),
         ("y_d", c_p), ("ldy", c_i64),
         ("partial_d", c_p), ("ldp", c_i64),
@@ -41,11 +41,11 @@ SIGNATURES = {
     "sgc_csr_check_canonical": (c_i32, [c_i64, c_i64, c_p, c_p, c_p, c_p]),
     "sgc_csr_canonicalize_workspace_bytes": (c_sz, [c_i64, c_i64]),
     "sgc_csr_canonicalize": (c_i32, [c_i64, c_i64, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_sz, c_p]),
-    "sgc_csr_selfloop_count": (c_i32, [c_i64, c_p, c_p, c_p, c_p, c_p, c_sz, c_p]),
-    "sgc_csr_selfloop_build": (c_i32, [c_i64, c_p, c_p, c_p, c_p, c_p, c_p, c_p]),
+    "sgc_csr_selfloop_count": (c_i32, [c_i64, c_i64, c_p, c_p, c_p, c_p, c_p, c_sz, c_p]),
+    "sgc_csr_selfloop_build": (c_i32, [c_i64, c_i64, c_p, c_p, c_p, c_p, c_p, c_p, c_p]),
     "sgc_degree_inv_sqrt": (c_i32, [c_i64, c_p, c_p, c_p, c_p, c_p]),
-    "sgc_norm_count": (c_i32, [c_i64, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_sz, c_p]),
-    "sgc_norm_build": (c_i32, [c_i64, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p]),
+    "sgc_norm_count": (c_i32, [c_i64, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_sz, c_p]),
+    "sgc_norm_build": (c_i32, [c_i64, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p]),
     "sgc_csr_to_coo": (c_i32, [c_i64, c_p, c_p, c_i64, c_p, c_p]),
     "sgc_coo_to_csr": (c_i32, [c_i64, c_i64, c_p, c_p, c_p, c_p, c_p, c_p]),
     "sgc_col_stats_workspace_bytes": (c_sz, [c_i64, c_i64]),

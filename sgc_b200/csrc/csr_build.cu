@@ -49,7 +49,7 @@ check_canonical_kernel(int64_t n_rows, int64_t n_cols, const int64_t *__restrict
 }
 
 __global__ void __launch_bounds__(ROW_THREADS)
-selfloop_count_kernel(int64_t n, const int64_t *__restrict__ row_ptr,
+selfloop_count_kernel(int64_t n, int64_t doff, const int64_t *__restrict__ row_ptr,
                       const int32_t *__restrict__ col, const double *__restrict__ val,
                       int64_t *__restrict__ counts)
 {
@@ -63,8 +63,8 @@ selfloop_count_kernel(int64_t n, const int64_t *__restrict__ row_ptr,
         for (int64_t p = b + gl; p < e; p += GRP) {
             const int32_t c = col[p];
             const double v = val[p];
-            diag |= (c == i);
-            cnt += keep_aug(i, c, v) ? 1 : 0;
+            diag |= (c == i + doff);
+            cnt += keep_aug(i + doff, c, v) ? 1 : 0;
         }
 #pragma unroll
         for (int o = GRP / 2; o > 0; o >>= 1) cnt += __shfl_xor_sync(gm, cnt, o);
@@ -75,7 +75,7 @@ selfloop_count_kernel(int64_t n, const int64_t *__restrict__ row_ptr,
 }
 
 __global__ void __launch_bounds__(ROW_THREADS)
-selfloop_build_kernel(int64_t n, const int64_t *__restrict__ row_ptr,
+selfloop_build_kernel(int64_t n, int64_t doff, const int64_t *__restrict__ row_ptr,
                       const int32_t *__restrict__ col, const double *__restrict__ val,
                       const int64_t *__restrict__ out_ptr, int32_t *__restrict__ col_out,
                       double *__restrict__ val_out)
@@ -86,9 +86,10 @@ selfloop_build_kernel(int64_t n, const int64_t *__restrict__ row_ptr,
     const int64_t groups = (int64_t)gridDim.x * ROWS_PER_BLOCK;
     for (int64_t i = (int64_t)blockIdx.x * ROWS_PER_BLOCK + threadIdx.x / GRP; i < n; i += groups) {
         const int64_t b = row_ptr[i], e = row_ptr[i + 1];
-        // does the row already store (i, i)?  (columns are unique, so at most once)
+        const int32_t dc = (int32_t)(i + doff);           // column of this row's diagonal
+        // does the row already store its diagonal?  (columns are unique, so at most once)
         bool diag = false;
-        for (int64_t p = b + gl; p < e; p += GRP) diag |= (col[p] == (int32_t)i);
+        for (int64_t p = b + gl; p < e; p += GRP) diag |= (col[p] == dc);
         const bool has_diag = (__ballot_sync(gm, diag) & gm) != 0u;
         int64_t w = out_ptr[i];          // next free output slot of the row
         bool diag_written = has_diag;    // nothing to insert when the diagonal is merged in place
@@ -100,11 +101,11 @@ selfloop_build_kernel(int64_t n, const int64_t *__restrict__ row_ptr,
             if (p < e) {
                 c = col[p];
                 v = val[p];
-                if (c == (int32_t)i) v += 1.0;              // a_ii + 1 (normalization.py:6)
+                if (c == dc) v += 1.0;                       // a_ii + 1 (normalization.py:6)
                 keep = (v != 0.0);                            // NaN != 0 is true: kept
             }
             // first lane whose column is past the diagonal: the self-loop goes in front of it
-            const unsigned past = (__ballot_sync(gm, p < e && c > (int32_t)i) & gm) >> gshift;
+            const unsigned past = (__ballot_sync(gm, p < e && c > dc) & gm) >> gshift;
             int ins_at = GRP;                                 // no insertion in this batch
             if (!diag_written && past) { ins_at = __ffs(past) - 1; diag_written = true; }
             const unsigned kept = (__ballot_sync(gm, keep) & gm) >> gshift;
@@ -112,13 +113,13 @@ selfloop_build_kernel(int64_t n, const int64_t *__restrict__ row_ptr,
             if (keep) { col_out[w + before] = c; val_out[w + before] = v; }
             if (ins_at < GRP && gl == ins_at) {
                 const int slot = __popc(kept & ((1u << gl) - 1u));
-                col_out[w + slot] = (int32_t)i;
+                col_out[w + slot] = dc;
                 val_out[w + slot] = 1.0;
             }
             w += __popc(kept) + (ins_at < GRP ? 1 : 0);
         }
         if (!diag_written && gl == 0) {                       // diagonal is the last entry of the row
-            col_out[w] = (int32_t)i;
+            col_out[w] = dc;
             val_out[w] = 1.0;
         }
     }
@@ -160,7 +161,8 @@ __device__ __forceinline__ bool keep_norm(double di, double a, double dj)
 
 __global__ void __launch_bounds__(ROW_THREADS)
 norm_count_kernel(int64_t n, const int64_t *__restrict__ row_ptr, const int32_t *__restrict__ col,
-                  const double *__restrict__ aval, const double *__restrict__ dinv,
+                  const double *__restrict__ aval, const double *__restrict__ dinv_rows,
+                  const double *__restrict__ dinv,
                   int64_t *__restrict__ counts, unsigned long long *__restrict__ dropped)
 {
     const int lane = threadIdx.x & 31, gl = lane & (GRP - 1);
@@ -169,7 +171,7 @@ norm_count_kernel(int64_t n, const int64_t *__restrict__ row_ptr, const int32_t 
     unsigned long long my_dropped = 0;
     for (int64_t i = (int64_t)blockIdx.x * ROWS_PER_BLOCK + threadIdx.x / GRP; i < n; i += groups) {
         const int64_t b = row_ptr[i], e = row_ptr[i + 1];
-        const double di = dinv[i];
+        const double di = dinv_rows[i];
         int cnt = 0;
         for (int64_t p = b + gl; p < e; p += GRP)
             cnt += keep_norm(di, aval[p], dinv[col[p]]) ? 1 : 0;
@@ -186,7 +188,8 @@ norm_count_kernel(int64_t n, const int64_t *__restrict__ row_ptr, const int32_t 
 
 __global__ void __launch_bounds__(ROW_THREADS)
 norm_build_kernel(int64_t n, const int64_t *__restrict__ row_ptr, const int32_t *__restrict__ col,
-                  const double *__restrict__ aval, const double *__restrict__ dinv,
+                  const double *__restrict__ aval, const double *__restrict__ dinv_rows,
+                  const double *__restrict__ dinv,
                   const int64_t *__restrict__ out_ptr, bool compact, int32_t *__restrict__ col_out,
                   double *__restrict__ aval_out, double *__restrict__ s64_out,
                   float *__restrict__ s32_out)
@@ -197,7 +200,7 @@ norm_build_kernel(int64_t n, const int64_t *__restrict__ row_ptr, const int32_t 
     const int64_t groups = (int64_t)gridDim.x * ROWS_PER_BLOCK;
     for (int64_t i = (int64_t)blockIdx.x * ROWS_PER_BLOCK + threadIdx.x / GRP; i < n; i += groups) {
         const int64_t b = row_ptr[i], e = row_ptr[i + 1];
-        const double di = dinv[i];
+        const double di = dinv_rows[i];
         int64_t w = compact ? out_ptr[i] : b;
         for (int64_t p0 = b; p0 < e; p0 += GRP) {
             const int64_t p = p0 + gl;
@@ -394,27 +397,28 @@ int32_t sgc_csr_canonicalize(int64_t n_rows, int64_t nnz, const int64_t *row_ptr
     return SGC_OK;
 }
 
-int32_t sgc_csr_selfloop_count(int64_t n, const int64_t *row_ptr_d, const int32_t *col_d,
-                               const double *val_d, int64_t *row_ptr_out_d, void *ws_d,
-                               size_t ws_bytes, void *stream)
+int32_t sgc_csr_selfloop_count(int64_t n, int64_t diag_offset, const int64_t *row_ptr_d,
+                               const int32_t *col_d, const double *val_d, int64_t *row_ptr_out_d,
+                               void *ws_d, size_t ws_bytes, void *stream)
 {
     SGC_REQUIRE(n >= 0 && row_ptr_d && row_ptr_out_d, "csr_selfloop_count: bad arguments");
     cudaStream_t s = as_stream(stream);
     selfloop_count_kernel<<<grid_for(ceil_div(n, ROWS_PER_BLOCK), 8), ROW_THREADS, 0, s>>>(
-        n, row_ptr_d, col_d, val_d, row_ptr_out_d);
+        n, diag_offset, row_ptr_d, col_d, val_d, row_ptr_out_d);
     SGC_LAUNCH_CHECK();
     return scan_exclusive_i64(row_ptr_out_d, n + 1, ws_d, ws_bytes, s);
 }
 
-int32_t sgc_csr_selfloop_build(int64_t n, const int64_t *row_ptr_d, const int32_t *col_d,
-                               const double *val_d, const int64_t *row_ptr_out_d,
-                               int32_t *col_out_d, double *aval_out_d, void *stream)
+int32_t sgc_csr_selfloop_build(int64_t n, int64_t diag_offset, const int64_t *row_ptr_d,
+                               const int32_t *col_d, const double *val_d,
+                               const int64_t *row_ptr_out_d, int32_t *col_out_d,
+                               double *aval_out_d, void *stream)
 {
     SGC_REQUIRE(n >= 0 && row_ptr_d && row_ptr_out_d, "csr_selfloop_build: bad arguments");
     if (n == 0) return SGC_OK;
     SGC_REQUIRE(col_out_d && aval_out_d, "csr_selfloop_build: null outputs");
     selfloop_build_kernel<<<grid_for(ceil_div(n, ROWS_PER_BLOCK), 8), ROW_THREADS, 0, as_stream(stream)>>>(
-        n, row_ptr_d, col_d, val_d, row_ptr_out_d, col_out_d, aval_out_d);
+        n, diag_offset, row_ptr_d, col_d, val_d, row_ptr_out_d, col_out_d, aval_out_d);
     SGC_LAUNCH_CHECK();
     return SGC_OK;
 }
@@ -431,29 +435,30 @@ int32_t sgc_degree_inv_sqrt(int64_t n, const int64_t *row_ptr_d, const double *a
 }
 
 int32_t sgc_norm_count(int64_t n, const int64_t *row_ptr_d, const int32_t *col_d,
-                       const double *aval_d, const double *dinv_d, int64_t *row_ptr_out_d,
-                       int64_t *dropped_d, void *ws_d, size_t ws_bytes, void *stream)
+                       const double *aval_d, const double *dinv_rows_d, const double *dinv_d,
+                       int64_t *row_ptr_out_d, int64_t *dropped_d, void *ws_d, size_t ws_bytes,
+                       void *stream)
 {
-    SGC_REQUIRE(n >= 0 && row_ptr_d && dinv_d && row_ptr_out_d && dropped_d, "norm_count: bad arguments");
+    SGC_REQUIRE(n >= 0 && row_ptr_d && dinv_d && dinv_rows_d && row_ptr_out_d && dropped_d, "norm_count: bad arguments");
     cudaStream_t s = as_stream(stream);
     SGC_CUDA_TRY(cudaMemsetAsync(dropped_d, 0, sizeof(int64_t), s));
     norm_count_kernel<<<grid_for(ceil_div(n, ROWS_PER_BLOCK), 8), ROW_THREADS, 0, s>>>(
-        n, row_ptr_d, col_d, aval_d, dinv_d, row_ptr_out_d,
+        n, row_ptr_d, col_d, aval_d, dinv_rows_d, dinv_d, row_ptr_out_d,
         reinterpret_cast<unsigned long long *>(dropped_d));
     SGC_LAUNCH_CHECK();
     return scan_exclusive_i64(row_ptr_out_d, n + 1, ws_d, ws_bytes, s);
 }
 
 int32_t sgc_norm_build(int64_t n, const int64_t *row_ptr_d, const int32_t *col_d,
-                       const double *aval_d, const double *dinv_d, const int64_t *row_ptr_out_d,
-                       int32_t *col_out_d, double *aval_out_d, double *s64_out_d,
-                       float *s32_out_d, void *stream)
+                       const double *aval_d, const double *dinv_rows_d, const double *dinv_d,
+                       const int64_t *row_ptr_out_d, int32_t *col_out_d, double *aval_out_d,
+                       double *s64_out_d, float *s32_out_d, void *stream)
 {
-    SGC_REQUIRE(n >= 0 && row_ptr_d && dinv_d && row_ptr_out_d, "norm_build: bad arguments");
+    SGC_REQUIRE(n >= 0 && row_ptr_d && dinv_d && dinv_rows_d && row_ptr_out_d, "norm_build: bad arguments");
     if (n == 0) return SGC_OK;
     const bool compact = (row_ptr_out_d != row_ptr_d);
     norm_build_kernel<<<grid_for(ceil_div(n, ROWS_PER_BLOCK), 8), ROW_THREADS, 0, as_stream(stream)>>>(
-        n, row_ptr_d, col_d, aval_d, dinv_d, row_ptr_out_d, compact, col_out_d, aval_out_d,
+        n, row_ptr_d, col_d, aval_d, dinv_rows_d, dinv_d, row_ptr_out_d, compact, col_out_d, aval_out_d,
         s64_out_d, s32_out_d);
     SGC_LAUNCH_CHECK();
     return SGC_OK;

@@ -180,6 +180,7 @@ static int32_t run_hop(const sgc_plan_impl *pl, const sgc_hop_args_t *a, const f
     HopDev p{};
     p.row_ptr = pl->row_ptr; p.col = pl->col;
     p.aval = a->aval_d; p.dinv = a->dinv_d; p.sval = a->sval_d;
+    p.dinv_rows = a->dinv_rows_d ? a->dinv_rows_d : a->dinv_d;
     p.x = x; p.ldx = ldx; p.y = y; p.ldy = ldy;
     p.partial = a->partial_d; p.ldp = a->ldp;
     p.mean = a->mean_d; p.stdv = a->std_d;

@@ -32,6 +32,7 @@ struct HopDev {
     const int32_t *col;
     const double *aval;
     const double *dinv;
+    const double *dinv_rows;
     const float *sval;
     const float *x;
     int64_t ldx;
@@ -227,7 +228,7 @@ spmm_hop_kernel(const HopDev p)
 #pragma unroll
         for (int v = 0; v < VEC; ++v) acc[u][v] = 0.f;
 
-    const double di = (FUSED && valid) ? p.dinv[row] : 0.0;
+    const double di = (FUSED && valid) ? p.dinv_rows[row] : 0.0;
     const int len = (int)(end - beg);
     const int nb = (len + G - 1) / G;
     const int nb_max = (GPW == 1) ? nb : __reduce_max_sync(0xffffffffu, nb);

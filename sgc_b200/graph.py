@@ -50,9 +50,10 @@ class SgcGraph(object):
 
     is_sparse = True
 
-    def __init__(self, n_rows, n_cols, row_ptr, col, aval, dinv, rowsum=None, sval=None):
+    def __init__(self, n_rows, n_cols, row_ptr, col, aval, dinv, rowsum=None, sval=None, dinv_rows=None):
         self.n_rows, self.n_cols = int(n_rows), int(n_cols)
         self.row_ptr, self.col, self.aval, self.dinv, self.rowsum = row_ptr, col, aval, dinv, rowsum
+        self.dinv_rows = dinv if dinv_rows is None else dinv_rows     # differs for a row slice only
         self.sval = sval                      # fp32 values of S when materialised (or given)
         self.nnz = int(col.numel())
         self.device = row_ptr.device
@@ -109,8 +110,8 @@ class SgcGraph(object):
             self.sval = torch.empty(self.nnz, dtype=torch.float32, device=self.device)
             with torch.cuda.device(self.device):
                 _ffi.call("sgc_norm_build", self.n_rows, _ffi.ptr(self.row_ptr), _ffi.ptr(self.col),
-                          _ffi.ptr(self.aval), _ffi.ptr(self.dinv), _ffi.ptr(self.row_ptr), None, None,
-                          None, _ffi.ptr(self.sval), stream_ptr())
+                          _ffi.ptr(self.aval), _ffi.ptr(self.dinv_rows), _ffi.ptr(self.dinv),
+                          _ffi.ptr(self.row_ptr), None, None, None, _ffi.ptr(self.sval), stream_ptr())
         return self.sval
 
     def values64(self):
@@ -118,8 +119,8 @@ class SgcGraph(object):
         out = torch.empty(self.nnz, dtype=torch.float64, device=self.device)
         with torch.cuda.device(self.device):
             _ffi.call("sgc_norm_build", self.n_rows, _ffi.ptr(self.row_ptr), _ffi.ptr(self.col),
-                      _ffi.ptr(self.aval), _ffi.ptr(self.dinv), _ffi.ptr(self.row_ptr), None, None,
-                      _ffi.ptr(out), None, stream_ptr())
+                      _ffi.ptr(self.aval), _ffi.ptr(self.dinv_rows), _ffi.ptr(self.dinv),
+                      _ffi.ptr(self.row_ptr), None, None, _ffi.ptr(out), None, stream_ptr())
         return out
 
     def coo_indices(self):
@@ -177,14 +178,14 @@ class _Plan(object):
 
 
 # ---- K1 + K2: normalisation driver ------------------------------------------------------------------
-def normalize_csr(n, row_ptr, col, val):
-    """``aug_normalized_adjacency`` on device CSR arrays (normalization.py:5-12).
-
-    row_ptr int64 [n+1], col int32 [nnz], val float64 [nnz], all on one CUDA device; any stored
-    order (non-canonical input is canonicalised first).  Returns an `SgcGraph`."""
+def augment_csr(n_rows, n_cols, row_offset, row_ptr, col, val):
+    """K1 + K2 on a row slice [row_offset, row_offset + n_rows) of an n_cols x n_cols adjacency with
+    global column ids (row_offset = 0 and n_rows == n_cols for a whole matrix): canonical CSR of
+    A + I (normalization.py:6) and the slice's row sums / D^-1/2 (normalization.py:8-10).
+    Returns (row_ptr, col, aval, rowsum, dinv_rows)."""
     dev = require_cuda(row_ptr.device)
     lib = _ffi.lib()
-    n = int(n)
+    n, n_cols, row_offset = int(n_rows), int(n_cols), int(row_offset)
     with torch.cuda.device(dev):
         s = stream_ptr()
         row_ptr = row_ptr.to(torch.int64).contiguous()
@@ -193,9 +194,9 @@ def normalize_csr(n, row_ptr, col, val):
         nnz = int(col.numel())
         scan_ws = _ws(lib.sgc_scan_workspace_bytes(n + 1), dev)
         flag = torch.empty(1, dtype=torch.int32, device=dev)
-        _ffi.call("sgc_csr_check_canonical", n, n, _ffi.ptr(row_ptr), _ffi.ptr(col), _ffi.ptr(flag), s)
+        _ffi.call("sgc_csr_check_canonical", n, n_cols, _ffi.ptr(row_ptr), _ffi.ptr(col), _ffi.ptr(flag), s)
         if int(flag.item()) == 0:
-            if nnz and (int(col.min().item()) < 0 or int(col.max().item()) >= n):
+            if nnz and (int(col.min().item()) < 0 or int(col.max().item()) >= n_cols):
                 raise ValueError("column index out of range")
             ws = _ws(lib.sgc_csr_canonicalize_workspace_bytes(n, nnz), dev)
             rp2 = torch.empty(n + 1, dtype=torch.int64, device=dev)
@@ -207,31 +208,54 @@ def normalize_csr(n, row_ptr, col, val):
             row_ptr, col, val = rp2, col2[:nnz], val2[:nnz]
         # K1: A + I
         rp_aug = torch.empty(n + 1, dtype=torch.int64, device=dev)
-        _ffi.call("sgc_csr_selfloop_count", n, _ffi.ptr(row_ptr), _ffi.ptr(col), _ffi.ptr(val),
+        _ffi.call("sgc_csr_selfloop_count", n, row_offset, _ffi.ptr(row_ptr), _ffi.ptr(col), _ffi.ptr(val),
                   _ffi.ptr(rp_aug), _ffi.ptr(scan_ws), scan_ws.numel(), s)
         nnz_aug = int(rp_aug[n].item()) if n else 0
         col_aug = torch.empty(nnz_aug, dtype=torch.int32, device=dev)
         aval = torch.empty(nnz_aug, dtype=torch.float64, device=dev)
-        _ffi.call("sgc_csr_selfloop_build", n, _ffi.ptr(row_ptr), _ffi.ptr(col), _ffi.ptr(val),
+        _ffi.call("sgc_csr_selfloop_build", n, row_offset, _ffi.ptr(row_ptr), _ffi.ptr(col), _ffi.ptr(val),
                   _ffi.ptr(rp_aug), _ffi.ptr(col_aug), _ffi.ptr(aval), s)
         # K2: degrees
         rowsum = torch.empty(n, dtype=torch.float64, device=dev)
         dinv = torch.empty(n, dtype=torch.float64, device=dev)
         _ffi.call("sgc_degree_inv_sqrt", n, _ffi.ptr(rp_aug), _ffi.ptr(aval), _ffi.ptr(rowsum),
                   _ffi.ptr(dinv), s)
-        # structure after scipy's zero-product pruning (only differs when some d_i == 0)
+    return rp_aug, col_aug, aval, rowsum, dinv
+
+
+def finish_normalization(n_rows, n_cols, rp_aug, col_aug, aval, rowsum, dinv_rows, dinv_cols):
+    """Structure of S after scipy's zero-product pruning (normalization.py:12; it only differs
+    from A + I when some D^-1/2 entry is zero) -> `SgcGraph`.  dinv_rows: D^-1/2 of the slice's
+    rows; dinv_cols: D^-1/2 of all n_cols columns."""
+    dev = require_cuda(rp_aug.device)
+    lib = _ffi.lib()
+    n = int(n_rows)
+    with torch.cuda.device(dev):
+        s = stream_ptr()
+        scan_ws = _ws(lib.sgc_scan_workspace_bytes(n + 1), dev)
         rp_s = torch.empty(n + 1, dtype=torch.int64, device=dev)
         dropped = torch.empty(1, dtype=torch.int64, device=dev)
-        _ffi.call("sgc_norm_count", n, _ffi.ptr(rp_aug), _ffi.ptr(col_aug), _ffi.ptr(aval), _ffi.ptr(dinv),
-                  _ffi.ptr(rp_s), _ffi.ptr(dropped), _ffi.ptr(scan_ws), scan_ws.numel(), s)
+        _ffi.call("sgc_norm_count", n, _ffi.ptr(rp_aug), _ffi.ptr(col_aug), _ffi.ptr(aval),
+                  _ffi.ptr(dinv_rows), _ffi.ptr(dinv_cols), _ffi.ptr(rp_s), _ffi.ptr(dropped),
+                  _ffi.ptr(scan_ws), scan_ws.numel(), s)
         if int(dropped.item()) != 0:
             nnz_s = int(rp_s[n].item())
             col_s = torch.empty(nnz_s, dtype=torch.int32, device=dev)
             aval_s = torch.empty(nnz_s, dtype=torch.float64, device=dev)
             _ffi.call("sgc_norm_build", n, _ffi.ptr(rp_aug), _ffi.ptr(col_aug), _ffi.ptr(aval),
-                      _ffi.ptr(dinv), _ffi.ptr(rp_s), _ffi.ptr(col_s), _ffi.ptr(aval_s), None, None, s)
+                      _ffi.ptr(dinv_rows), _ffi.ptr(dinv_cols), _ffi.ptr(rp_s), _ffi.ptr(col_s),
+                      _ffi.ptr(aval_s), None, None, s)
             rp_aug, col_aug, aval = rp_s, col_s, aval_s
-    return SgcGraph(n, n, rp_aug, col_aug, aval, dinv, rowsum=rowsum)
+    return SgcGraph(n, int(n_cols), rp_aug, col_aug, aval, dinv_cols, rowsum=rowsum, dinv_rows=dinv_rows)
+
+
+def normalize_csr(n, row_ptr, col, val):
+    """``aug_normalized_adjacency`` on device CSR arrays (normalization.py:5-12).
+
+    row_ptr int64 [n+1], col int32 [nnz], val float64 [nnz], all on one CUDA device; any stored
+    order (non-canonical input is canonicalised first).  Returns an `SgcGraph`."""
+    rp_aug, col_aug, aval, rowsum, dinv = augment_csr(n, n, 0, row_ptr, col, val)
+    return finish_normalization(n, n, rp_aug, col_aug, aval, rowsum, dinv, dinv)
 
 
 def upload_csr(adj, device=None):

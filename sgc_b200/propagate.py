@@ -68,7 +68,7 @@ def _hop_args(g, plan, x, ldx, y, ldy, f, partial, mean, std, std_mode, slab, hi
     flags = 0
     if g.fused:
         flags |= _ffi.HOP_FUSED_NORM
-        a.aval_d, a.dinv_d = _ffi.ptr(g.aval), _ffi.ptr(g.dinv)
+        a.aval_d, a.dinv_d, a.dinv_rows_d = _ffi.ptr(g.aval), _ffi.ptr(g.dinv), _ffi.ptr(g.dinv_rows)
     else:
         a.sval_d = _ffi.ptr(g.sval)
     if mean is not None:

@@ -1,0 +1,95 @@
+"""Host-side logic of the row-sharded propagation (sgc_b200/dist.py) on CPU: world_size 2 and 3
+over gloo.  The CUDA hop is replaced by the oracle's CPU hop (tests may use the oracle), so what
+is exercised is the partition, the slab-major packing, the per-slab all-gather pipeline and its
+ordering across hops.  Results must equal the single-process oracle bit for bit."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+
+def free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def make_problem(n=53, f=70, seed=0):
+    from oracle import normalization_oracle as no
+    rng = np.random.RandomState(seed)
+    dense = (rng.rand(n, n) < 0.15).astype(np.float64)
+    dense = np.maximum(dense, dense.T)
+    np.fill_diagonal(dense, 0)
+    dense[7, :] = 1.0                                  # a hub row
+    dense[:, 7] = 1.0
+    indptr = np.zeros(n + 1, dtype=np.int64)
+    rows, cols = np.nonzero(dense)
+    np.cumsum(np.bincount(rows, minlength=n), out=indptr[1:])
+    r = no.aug_normalized_adjacency_oracle(n, indptr, cols.astype(np.int32), dense[rows, cols])
+    x = rng.standard_normal((n, f)).astype(np.float32)
+    return r["indptr"], r["indices"].astype(np.int32), r["data"].astype(np.float32), x
+
+
+def worker(rank, world, port, k, slab_w, ret):
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from oracle import spmm_oracle as so
+        from sgc_b200 import dist as sd
+        from sgc_b200.graph import SgcGraph
+        indptr, indices, data, x = make_problem()
+        n, f = x.shape
+        n_pad, parts = sd.partition_rows(n, world)
+        row0, row1 = parts[rank]
+        b, e = indptr[row0], indptr[row1]
+        g = SgcGraph(row1 - row0, world * n_pad, torch.from_numpy(indptr[row0:row1 + 1] - b),
+                     torch.from_numpy(indices[b:e]), None, None, sval=torch.from_numpy(data[b:e]))
+        sg = sd.ShardedGraph(g, rank, world, n, n_pad, row0, row1)
+        calls = []
+
+        def cpu_hop(graph, xin, out):
+            calls.append(tuple(xin.shape))
+            y = so.spmm_hop(graph.row_ptr.numpy(), graph.col.numpy(), graph.sval.numpy(),
+                            np.ascontiguousarray(xin.numpy()))
+            out.copy_(torch.from_numpy(y))
+
+        y = sd.propagate_sharded(sg, torch.from_numpy(x[row0:row1].copy()), k, slab_w=slab_w, hop_fn=cpu_hop)
+        assert len(calls) == k * ((f + slab_w - 1) // slab_w)
+        assert all(c[0] == world * n_pad for c in calls)
+        ret[rank] = (row0, row1, y.numpy().copy())
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,k,slab_w", [(2, 2, 32), (2, 3, 64), (3, 1, 32), (3, 3, 128)])
+def test_sharded_pipeline_matches_single_process(world, k, slab_w):
+    from oracle import spmm_oracle as so
+    indptr, indices, data, x = make_problem()
+    want, _ = so.sgc_precompute_oracle(x, indptr, indices, data, k)
+    ret = mp.Manager().dict()
+    mp.spawn(worker, args=(world, free_port(), k, slab_w, ret), nprocs=world, join=True)
+    got = np.zeros_like(want)
+    covered = 0
+    for rank in range(world):
+        row0, row1, y = ret[rank]
+        got[row0:row1] = y
+        covered += row1 - row0
+    assert covered == x.shape[0]
+    assert np.array_equal(got, want)
+
+
+def test_partition_rows():
+    from sgc_b200.dist import partition_rows
+    for n, world in ((10, 4), (5, 4), (8, 8), (2449029, 8), (1, 2)):
+        n_pad, parts = partition_rows(n, world)
+        assert len(parts) == world and parts[0][0] == 0 and parts[-1][1] == n
+        assert all(a[1] == b[0] for a, b in zip(parts, parts[1:]))
+        assert all(0 <= r1 - r0 <= n_pad for r0, r1 in parts)
+        # a global row id is its own index in the gathered operand
+        for rank, (r0, r1) in enumerate(parts):
+            if r1 > r0:
+                assert r0 == rank * n_pad
