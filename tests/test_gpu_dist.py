@@ -34,7 +34,7 @@ def worker(rank, world, port, scale, f, k, slab_w, ret):
         row0, row1 = parts[rank]
         rp, col, val = sd.local_rows_of((s["row_ptr"], s["col"], s["val"]), row0, row1)
         sg = sd.shard_normalize(n, rp, col, val)
-        y = sd.propagate_sharded(sg, x[row0:row1].contiguous(), k, slab_w=slab_w)
+        y = sd.propagate_sharded(sg, x[row0:row1].contiguous(), k, row_blocks=slab_w)
         # single-GPU result on the same device
         full = sgc_b200.normalize_csr(n, s["row_ptr"], s["col"], s["val"])
         want, _ = sgc_b200.sgc_precompute(x, full, k)
@@ -47,7 +47,7 @@ def worker(rank, world, port, scale, f, k, slab_w, ret):
 
 def run(world, **kw):
     ret = mp.Manager().dict()
-    args = (world, free_port(), kw.get("scale", 0.02), kw.get("f", 100), kw.get("k", 3), kw.get("slab_w", 32), ret)
+    args = (world, free_port(), kw.get("scale", 0.02), kw.get("f", 100), kw.get("k", 3), kw.get("slab_w", 4), ret)
     mp.spawn(worker, args=args, nprocs=world, join=True)
     for rank in range(world):
         ok, same_struct, same_d, rows = ret[rank]
@@ -58,12 +58,12 @@ def run(world, **kw):
 def test_sharded_world1_bit_identical():
     if not torch.cuda.is_available():
         pytest.skip("no CUDA device")
-    run(1, f=100, k=3, slab_w=32)
-    run(1, f=602, k=2, slab_w=128)
+    run(1, f=100, k=3, slab_w=4)
+    run(1, f=602, k=2, slab_w=1)
 
 
 def test_sharded_world2_bit_identical():
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
-    run(2, f=100, k=3, slab_w=32)
-    run(2, f=130, k=2, slab_w=64)
+    run(2, f=100, k=3, slab_w=4)
+    run(2, f=130, k=2, slab_w=3)
