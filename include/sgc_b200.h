@@ -149,6 +149,8 @@ void    sgc_spmm_plan_destroy(sgc_plan_t *plan);
 /* Number of long-row chunk items (rows of the partial-sum buffer a hop needs). */
 int64_t sgc_spmm_plan_partial_rows(const sgc_plan_t *plan);
 
+#define SGC_MAX_PEERS        15   /* GPUs of one NVLink domain minus this one                       */
+
 #define SGC_HOP_FUSED_NORM   1u   /* weights = fp32((d_i*a_ij)*d_j) on the fly from aval_d + dinv_d */
 #define SGC_HOP_STD_DIV      2u   /* gathered x -> (x - mean[f]) / std[f]   (exact, utils.py:119)   */
 #define SGC_HOP_STD_RCP      4u   /* gathered x -> (x - mean[f]) * (1/std[f])  (<= 1 ulp from DIV)   */
@@ -171,6 +173,14 @@ typedef struct sgc_hop_args {
     uint32_t      flags;
     int32_t       hints;       /* bit0: L2 evict_last policy on gathered x rows; bit1: evict_first on
                                   the streamed col/value reads and the y stores                  */
+    /* Row-sharded multi-GPU hop (K5): every output row is ALSO stored, from the registers of the
+     * SpMM epilogue, to the same (row, column) offset of n_peers other buffers -- the peers'
+     * copies of the gathered operand of the next hop, mapped into this process with
+     * sgc_ipc_open() and reached over NVLink.  peer_y_d[p] corresponds to y_d (same logical row
+     * 0, same leading dimension ldy).  n_peers = 0 for a single-GPU hop. */
+    int32_t       n_peers;
+    int32_t       reserved_;
+    float        *peer_y_d[SGC_MAX_PEERS];
 } sgc_hop_args_t;
 
 /* One hop Y = S X on `stream`. */
@@ -181,6 +191,26 @@ int32_t sgc_spmm_hop(const sgc_plan_t *plan, const sgc_hop_args_t *args, void *s
  * args->y_d.  The standardisation flags apply to the first hop only.  Square matrices only. */
 int32_t sgc_precompute(const sgc_plan_t *plan, const sgc_hop_args_t *args, int32_t k_hops,
                        float *buf_a_d, float *buf_b_d, int64_t ld_buf, void *stream);
+
+/* ---- K5: row-sharded multi-GPU propagation (north_star (3); no counterpart in the reference) ---
+ * One process per GPU.  Every rank owns a contiguous row range of S and keeps two full-height
+ * gathered operands (ping-pong).  The hop kernel itself pushes each output row to every peer
+ * (sgc_hop_args.peer_y_d) while it computes, so there is no separate all-gather; the ranks only
+ * meet at a barrier between hops.  The operands live in "symmetric" buffers allocated here with
+ * cudaMalloc (the one place the library allocates device memory: a cudaIpc handle must cover a
+ * whole allocation) and exchanged between the processes as 64-byte CUDA IPC handles. */
+int32_t sgc_symm_alloc(size_t bytes, void **ptr_out);      /* zero-filled; synchronises          */
+int32_t sgc_symm_free(void *ptr_d);
+#define SGC_IPC_HANDLE_BYTES 64
+int32_t sgc_ipc_export(void *ptr_d, void *handle_out /* 64 bytes, host */);
+/* Maps a peer process's allocation into this process (enables peer access lazily). */
+int32_t sgc_ipc_open(const void *handle /* 64 bytes, host */, void **ptr_out);
+int32_t sgc_ipc_close(void *ptr_d);
+/* dst_d[p] <- src_d for p < n_dst (row-major [rows, f] pieces with leading dimensions ld_src /
+ * ld_dst): distributes this rank's rows of the initial features to every peer in one kernel. */
+int32_t sgc_push_rows(const float *src_d, int64_t ld_src, int64_t rows, int32_t f,
+                      float *const *dst_d /* host array of n_dst device pointers */, int32_t n_dst,
+                      int64_t ld_dst, void *stream);
 
 #ifdef __cplusplus
 }

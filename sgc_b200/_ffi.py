@@ -16,6 +16,8 @@ c_i32, c_i64, c_u32, c_sz, c_p = (ctypes.c_int32, ctypes.c_int64, ctypes.c_uint3
 HOP_FUSED_NORM = 1
 HOP_STD_DIV = 2
 HOP_STD_RCP = 4
+MAX_PEERS = 15
+IPC_HANDLE_BYTES = 64
 
 
 class HopArgs(ctypes.Structure):
@@ -27,6 +29,7 @@ class HopArgs(ctypes.Structure):
         ("partial_d", c_p), ("ldp", c_i64),
         ("mean_d", c_p), ("std_d", c_p),
         ("f", c_i32), ("slab_floats", c_i32), ("flags", c_u32), ("hints", c_i32),
+        ("n_peers", c_i32), ("reserved_", c_i32), ("peer_y_d", c_p * 15),
     ]
 
 
@@ -58,6 +61,12 @@ SIGNATURES = {
     "sgc_spmm_plan_partial_rows": (c_i64, [c_p]),
     "sgc_spmm_hop": (c_i32, [c_p, ctypes.POINTER(HopArgs), c_p]),
     "sgc_precompute": (c_i32, [c_p, ctypes.POINTER(HopArgs), c_i32, c_p, c_p, c_i64, c_p]),
+    "sgc_symm_alloc": (c_i32, [c_sz, ctypes.POINTER(c_p)]),
+    "sgc_symm_free": (c_i32, [c_p]),
+    "sgc_ipc_export": (c_i32, [c_p, c_p]),
+    "sgc_ipc_open": (c_i32, [c_p, ctypes.POINTER(c_p)]),
+    "sgc_ipc_close": (c_i32, [c_p]),
+    "sgc_push_rows": (c_i32, [c_p, c_i64, c_i64, c_i32, ctypes.POINTER(c_p), c_i32, c_i64, c_p]),
 }
 
 _lib = None

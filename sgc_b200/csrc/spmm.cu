@@ -6,15 +6,15 @@
 
 namespace sgc {
 
-hop_launch_fn find_hop_kernel_v4(int g, int u, bool fused, int stdmode);
-hop_launch_fn find_hop_kernel_v2(int g, int u, bool fused, int stdmode);
-hop_launch_fn find_hop_kernel_v1(int g, int u, bool fused, int stdmode);
+hop_launch_fn find_hop_kernel_v4(int g, int u, bool fused, int stdmode, bool peers);
+hop_launch_fn find_hop_kernel_v2(int g, int u, bool fused, int stdmode, bool peers);
+hop_launch_fn find_hop_kernel_v1(int g, int u, bool fused, int stdmode, bool peers);
 
-hop_launch_fn find_hop_kernel(int g, int vec, int u, bool fused, int stdmode)
+hop_launch_fn find_hop_kernel(int g, int vec, int u, bool fused, int stdmode, bool peers)
 {
-    if (vec == 4) return find_hop_kernel_v4(g, u, fused, stdmode);
-    if (vec == 2) return find_hop_kernel_v2(g, u, fused, stdmode);
-    if (vec == 1) return find_hop_kernel_v1(g, u, fused, stdmode);
+    if (vec == 4) return find_hop_kernel_v4(g, u, fused, stdmode, peers);
+    if (vec == 2) return find_hop_kernel_v2(g, u, fused, stdmode, peers);
+    if (vec == 1) return find_hop_kernel_v1(g, u, fused, stdmode, peers);
     return nullptr;
 }
 
@@ -61,13 +61,15 @@ plan_fill_kernel(int64_t n, const int64_t *__restrict__ row_ptr, int32_t chunk,
     }
 }
 
+struct PeerList { int32_t n; float *y[SGC_MAX_PEERS]; };
+
 // y[row] = partial[first] + partial[first+1] + ... in chunk order; one thread per
 // (long row, feature), consecutive threads on consecutive features.
 __global__ void __launch_bounds__(256)
 spmm_fixup_kernel(int64_t n_long_rows, const int32_t *__restrict__ lr_row,
                   const int64_t *__restrict__ lr_first, const int32_t *__restrict__ lr_cnt,
                   const float *__restrict__ partial, int64_t ldp, float *__restrict__ y,
-                  int64_t ldy, int32_t f)
+                  int64_t ldy, int32_t f, PeerList peers)
 {
     const int64_t k = blockIdx.x;
     if (k >= n_long_rows) return;
@@ -77,6 +79,7 @@ spmm_fixup_kernel(int64_t n_long_rows, const int32_t *__restrict__ lr_row,
         float acc = partial[first * ldp + c];
         for (int j = 1; j < cnt; ++j) acc = __fadd_rn(acc, partial[(first + j) * ldp + c]);
         y[row * ldy + c] = acc;
+        for (int pp = 0; pp < peers.n; ++pp) peers.y[pp][row * ldy + c] = acc;   // K5 push
     }
 }
 
@@ -109,24 +112,32 @@ static PlanLayout plan_layout(int64_t n_rows, int64_t nnz, int32_t chunk)
     return L;
 }
 
-// Default slab width (floats) for a gathered operand of n_cols rows: the widest slab whose
-// N x SW x 4-byte working set fits the L2 budget; whole rows when everything fits.
+// Default slab width (floats) for a gathered operand of n_cols rows.
+//   * everything fits in L2, or nothing does: whole rows (one pass over col/val, the longest
+//     contiguous gathers).  Measured on B200, products shape (N = 2.45 M, F = 100, X = 980 MB):
+//     whole rows 9.3 ms per hop, 64-float slabs 13.8 ms, 32-float slabs 20 ms.
+//   * otherwise the widest slab whose N x SW x 4-byte working set fits the L2 budget, so the
+//     slab stays resident while all rows sweep over it (Reddit shape: 128 floats = 119 MB,
+//     5.0 ms per hop; see profiles/ for the sweep over 32..256).
+constexpr double L2_SLAB_BUDGET = 128.0 * 1024 * 1024;
+
+static bool slab_fits_l2(int64_t n_cols, int slab) { return (double)n_cols * slab * 4.0 <= L2_SLAB_BUDGET; }
+
 static int default_slab(int64_t n_cols, int f, int vec)
 {
-    const double budget = 128.0 * 1024 * 1024;     // measured on B200 (Reddit shape): 119 MB slab beats 60 MB and 238 MB
     const int widths4[] = {256, 128, 64, 32};
     const int widths2[] = {128, 64, 32};
     const int widths1[] = {64, 32};
     const int *w = vec == 4 ? widths4 : (vec == 2 ? widths2 : widths1);
     const int nw = vec == 4 ? 4 : (vec == 2 ? 3 : 2);
-    int best = w[nw - 1];
-    for (int i = nw - 1; i >= 0; --i) {
-        if ((double)n_cols * w[i] * 4.0 <= budget) best = w[i];
-    }
-    // never wider than needed to cover f in one slab
-    for (int i = nw - 1; i >= 0; --i)
-        if (w[i] >= f && w[i] < best) best = w[i];
-    return best;
+    // narrowest built width that covers f in one slab (or the widest one if none does)
+    int whole = w[0];
+    for (int i = 0; i < nw; ++i)
+        if (w[i] >= f) whole = w[i];
+    int best = 0;
+    for (int i = 0; i < nw; ++i)               // widest first
+        if (w[i] <= whole && slab_fits_l2(n_cols, w[i])) { best = w[i]; break; }
+    return best ? best : whole;
 }
 
 static bool slab_shape(int slab, int vec, int *g, int *u)
@@ -138,7 +149,8 @@ static bool slab_shape(int slab, int vec, int *g, int *u)
 }
 
 static int32_t run_hop(const sgc_plan_impl *pl, const sgc_hop_args_t *a, const float *x,
-                       int64_t ldx, float *y, int64_t ldy, uint32_t flags, cudaStream_t s)
+                       int64_t ldx, float *y, int64_t ldy, uint32_t flags, bool push_peers,
+                       cudaStream_t s)
 {
     const bool fused = (flags & SGC_HOP_FUSED_NORM) != 0;
     const int stdmode = (flags & SGC_HOP_STD_DIV) ? 1 : ((flags & SGC_HOP_STD_RCP) ? 2 : 0);
@@ -170,10 +182,11 @@ static int32_t run_hop(const sgc_plan_impl *pl, const sgc_hop_args_t *a, const f
             return SGC_ERR_UNSUPPORTED;
         }
     }
-    hop_launch_fn fn = find_hop_kernel(g, vec, u, fused, stdmode);
+    const bool peers_on = push_peers && a->n_peers > 0;
+    hop_launch_fn fn = find_hop_kernel(g, vec, u, fused, stdmode, peers_on);
     if (!fn) {
-        set_error("spmm_hop: kernel variant g=%d vec=%d u=%d fused=%d std=%d not built", g, vec, u,
-                  (int)fused, stdmode);
+        set_error("spmm_hop: kernel variant g=%d vec=%d u=%d fused=%d std=%d peers=%d not built", g, vec, u,
+                  (int)fused, stdmode, (int)peers_on);
         return SGC_ERR_UNSUPPORTED;
     }
 
@@ -190,12 +203,22 @@ static int32_t run_hop(const sgc_plan_impl *pl, const sgc_hop_args_t *a, const f
     p.n_slabs = (a->f + slab - 1) / slab;
     p.y_vec = y_vec;
     p.hints = a->hints & 3;
+    // keeping gathered rows with evict_last only helps when the slab can actually stay in L2
+    if (!slab_fits_l2(pl->n_cols, slab < a->f ? slab : a->f)) p.hints &= ~1;
+    SGC_REQUIRE(a->n_peers >= 0 && a->n_peers <= SGC_MAX_PEERS, "spmm_hop: n_peers out of range");
+    p.n_peers = push_peers ? a->n_peers : 0;
+    PeerList peers{};
+    peers.n = p.n_peers;
+    for (int i = 0; i < p.n_peers; ++i) {
+        SGC_REQUIRE(a->peer_y_d[i] != nullptr, "spmm_hop: peer_y_d[%d] is null", i);
+        p.peer_y[i] = peers.y[i] = a->peer_y_d[i];
+    }
     const int64_t n_tasks = (int64_t)p.n_slabs * (p.n_long_items + p.n_rows);
     int32_t rc = fn(p, n_tasks, s);
     if (rc != SGC_OK) return rc;
     if (pl->n_long_rows > 0) {
         spmm_fixup_kernel<<<(unsigned)pl->n_long_rows, 256, 0, s>>>(
-            pl->n_long_rows, pl->lr_row, pl->lr_first, pl->lr_cnt, a->partial_d, a->ldp, y, ldy, a->f);
+            pl->n_long_rows, pl->lr_row, pl->lr_first, pl->lr_cnt, a->partial_d, a->ldp, y, ldy, a->f, peers);
         SGC_LAUNCH_CHECK();
     }
     return SGC_OK;
@@ -288,7 +311,7 @@ int64_t sgc_spmm_plan_partial_rows(const sgc_plan_t *plan) { return plan ? plan-
 int32_t sgc_spmm_hop(const sgc_plan_t *plan, const sgc_hop_args_t *args, void *stream)
 {
     SGC_REQUIRE(plan && args, "spmm_hop: null plan or args");
-    return run_hop(&plan->impl, args, args->x_d, args->ldx, args->y_d, args->ldy, args->flags,
+    return run_hop(&plan->impl, args, args->x_d, args->ldx, args->y_d, args->ldy, args->flags, true,
                    as_stream(stream));
 }
 
@@ -309,7 +332,7 @@ int32_t sgc_precompute(const sgc_plan_t *plan, const sgc_hop_args_t *args, int32
         float *dst = last ? args->y_d : ((k & 1) ? buf_b_d : buf_a_d);
         const int64_t ld_dst = last ? args->ldy : ld_buf;
         const uint32_t flags = (k == 0) ? args->flags : (args->flags & ~std_bits);
-        int32_t rc = run_hop(&plan->impl, args, src, ld_src, dst, ld_dst, flags, s);
+        int32_t rc = run_hop(&plan->impl, args, src, ld_src, dst, ld_dst, flags, false, s);
         if (rc != SGC_OK) return rc;
         src = dst;
         ld_src = ld_dst;

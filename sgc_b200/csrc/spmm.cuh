@@ -52,6 +52,8 @@ struct HopDev {
     int32_t n_slabs;
     int32_t y_vec;       // widest legal vector store into y (1, 2 or 4 floats)
     int32_t hints;       // bit0: L2 evict_last on gathered rows; bit1: evict_first on streams
+    int32_t n_peers;     // K5: copies of y in other GPUs' memory that receive every output row
+    float *peer_y[SGC_MAX_PEERS];
 };
 
 struct sgc_plan_impl {
@@ -71,7 +73,7 @@ struct sgc_plan_impl {
 typedef int32_t (*hop_launch_fn)(const HopDev &, int64_t n_tasks, cudaStream_t);
 
 // Filled by the instantiation units (spmm_inst_*.cu).
-hop_launch_fn find_hop_kernel(int g, int vec, int u, bool fused, int stdmode);
+hop_launch_fn find_hop_kernel(int g, int vec, int u, bool fused, int stdmode, bool peers);
 
 #ifdef __CUDACC__
 
@@ -151,6 +153,21 @@ __device__ __forceinline__ void st_hint_v1(float *p, float v, uint64_t pol)
     asm volatile("st.global.L2::cache_hint.f32 [%0], %1, %2;" :: "l"(p), "f"(v), "l"(pol) : "memory");
 }
 
+// Plain stores for peer (NVLink-mapped) addresses: cache policies do not apply to them.
+__device__ __forceinline__ void st_peer_v4(float *p, const float *v)
+{
+    asm volatile("st.global.v4.f32 [%0], {%1,%2,%3,%4};"
+                 :: "l"(p), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]) : "memory");
+}
+__device__ __forceinline__ void st_peer_v2(float *p, const float *v)
+{
+    asm volatile("st.global.v2.f32 [%0], {%1,%2};" :: "l"(p), "f"(v[0]), "f"(v[1]) : "memory");
+}
+__device__ __forceinline__ void st_peer_v1(float *p, float v)
+{
+    asm volatile("st.global.f32 [%0], %1;" :: "l"(p), "f"(v) : "memory");
+}
+
 // STD: 0 none, 1 exact division, 2 multiply by reciprocal
 template <int STD>
 __device__ __forceinline__ float standardize(float x, float mu, float s)
@@ -160,7 +177,7 @@ __device__ __forceinline__ float standardize(float x, float mu, float s)
     return x;
 }
 
-template <int G, int VEC, int U, bool FUSED, int STD>
+template <int G, int VEC, int U, bool FUSED, int STD, bool PEERS>
 __global__ void __launch_bounds__(HOP_THREADS, 5)
 spmm_hop_kernel(const HopDev p)
 {
@@ -308,9 +325,34 @@ spmm_hop_kernel(const HopDev p)
                 if (fo[u] + v < p.f) st_hint_v1(q + v, acc[u][v], pol_y);
         }
     }
+    // K5: the same registers go to every peer's copy of the next hop's gathered operand.  The
+    // stores are fire-and-forget NVLink writes issued while other warps are still gathering, so
+    // the exchange overlaps the SpMM inside one kernel.
+    if (PEERS && to_y && p.n_peers > 0) {
+        const int64_t off = row * p.ldy;
+        for (int pp = 0; pp < p.n_peers; ++pp) {
+            float *base = p.peer_y[pp] + off;
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                if (!act[u]) continue;
+                float *q = base + fo[u];
+                if (VEC == 4 && sv == 4) {
+                    st_peer_v4(q, acc[u]);
+                } else if (VEC >= 2 && sv >= 2) {
+#pragma unroll
+                    for (int v = 0; v < VEC; v += 2)
+                        if (fo[u] + v < p.f) st_peer_v2(q + v, &acc[u][v]);
+                } else {
+#pragma unroll
+                    for (int v = 0; v < VEC; ++v)
+                        if (fo[u] + v < p.f) st_peer_v1(q + v, acc[u][v]);
+                }
+            }
+        }
+    }
 }
 
-template <int G, int VEC, int U, bool FUSED, int STD>
+template <int G, int VEC, int U, bool FUSED, int STD, bool PEERS>
 int32_t launch_hop(const HopDev &p, int64_t n_tasks, cudaStream_t s)
 {
     constexpr int GPW = 32 / G;
@@ -321,7 +363,7 @@ int32_t launch_hop(const HopDev &p, int64_t n_tasks, cudaStream_t s)
         set_error("spmm_hop: grid too large (%lld blocks)", (long long)blocks);
         return SGC_ERR_INVALID;
     }
-    spmm_hop_kernel<G, VEC, U, FUSED, STD><<<(unsigned)blocks, HOP_THREADS, 0, s>>>(p);
+    spmm_hop_kernel<G, VEC, U, FUSED, STD, PEERS><<<(unsigned)blocks, HOP_THREADS, 0, s>>>(p);
     SGC_LAUNCH_CHECK();
     return SGC_OK;
 }

@@ -7,23 +7,33 @@ and of D^-1/2, produces those rows of every hop's output, and the hops exchange 
 Data layout.  Every rank keeps two full-height gathered operands ``buf[0|1]`` of shape
 [world*n_pad, ld] (row-major, ld = F rounded up to 8 floats).  Hop k gathers from buf[k%2] and
 writes this rank's rows straight into its own segment of buf[(k+1)%2]; the other segments of
-that buffer are filled by the exchange.  A global row id is its own index in the buffer, so the
+that buffer are filled by the peers.  A global row id is its own index in the buffer, so the
 single-GPU kernel runs unchanged and every output element is accumulated in the same order as on
 one GPU: sharded results are bit-identical to single-GPU results for any GPU count.
 
-Exchange fused with the hop as one pipeline over ROW BLOCKS: this rank's rows are cut into R
-blocks; as soon as the SpMM of block r has been enqueued, its output rows are sent to every peer
-(one NCCL group of sends/receives per block, placed directly at their final position) while the
-SpMM of block r+1.. keeps the SMs busy.  Only the last block's transfer is exposed, i.e. 1/R of
-the per-hop NVLink time.  Measured alternatives are in DESIGN.md (feature-slab pipelining is far
-slower for F=100 because narrow slabs re-read col/val and gather 128-byte pieces).
+Two ways of filling the peers' segments:
+
+``push`` (default on CUDA)  the exchange is fused into the SpMM kernel.  The operands are
+    "symmetric" buffers (sgc_symm_alloc) whose CUDA IPC handles the ranks swap once; every rank
+    maps every peer's buffers into its own address space.  spmm_hop_kernel then stores each
+    output row from its epilogue registers to the local buffer AND to the same offset of every
+    peer's buffer over NVLink (sgc_hop_args.peer_y_d) while other warps are still gathering: one
+    kernel per hop, no all-gather, and the ranks only meet at a tiny barrier between hops.
+
+``exchange``  one NCCL group of sends/receives per ROW BLOCK, placed directly at their final
+    position, pipelined with the SpMM of the following blocks (only the last block's transfer is
+    exposed).  Library-collective baseline for the fused path; also the mode the CPU (gloo) tests
+    drive.
 """
+import ctypes
 import os
 import time
+import weakref
 
 import torch
 import torch.distributed as dist
 
+from . import _ffi
 from .graph import SgcGraph, augment_csr, finish_normalization
 
 
@@ -71,33 +81,105 @@ def shard_normalize(n_global, row_ptr_local, col, val, group=None):
 
 
 def default_row_blocks():
-    """Pipeline stages per hop (SGC_B200_DIST_BLOCKS)."""
+    """Pipeline stages per hop in ``exchange`` mode (SGC_B200_DIST_BLOCKS)."""
     return max(1, int(os.environ.get("SGC_B200_DIST_BLOCKS", "4")))
 
 
-def _cuda_hop(graph, x, out):
+def default_mode(device):
+    """SGC_B200_DIST_MODE: 'push' (fused into the hop kernel; CUDA only) or 'exchange'."""
+    mode = os.environ.get("SGC_B200_DIST_MODE", "push" if torch.device(device).type == "cuda" else "exchange")
+    if mode not in ("push", "exchange"):
+        raise ValueError("SGC_B200_DIST_MODE must be 'push' or 'exchange'")
+    return mode
+
+
+def _cuda_hop(graph, x, out, peers=None):
     from .propagate import hop
-    hop(graph, x, out=out)
+    hop(graph, x, out=out, peers=peers)
 
 
 def _pad8(f):
     return (f + 7) // 8 * 8
 
 
-class ShardedPropagator(object):
-    """Buffers + pipeline for K-hop propagation on a ShardedGraph (see module docstring)."""
+class _DeviceMemory(object):
+    """Lets torch.as_tensor view a raw device allocation (CUDA array interface, no copy)."""
 
-    def __init__(self, sg, f, row_blocks=None, group=None, hop_fn=None):
+    def __init__(self, ptr, shape):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": "<f4", "data": (int(ptr), False),
+                                         "version": 2, "strides": None}
+
+
+def _release_symm(local_ptr, peer_ptrs):
+    lib = _ffi.lib()
+    for ptr in peer_ptrs:
+        lib.sgc_ipc_close(ptr)
+    lib.sgc_symm_free(local_ptr)
+
+
+class SymmetricBuffer(object):
+    """fp32 [rows, ld] buffer that exists on every rank of the group at the same logical layout,
+    each rank holding device addresses of all of them: ``ptrs[r]`` is rank r's copy as seen from
+    this process (its own allocation for r == rank, a CUDA-IPC mapping reached over NVLink
+    otherwise).  Collective: every rank of the group must construct it at the same time."""
+
+    def __init__(self, rows, ld, device, group=None):
+        lib = _ffi.lib()
+        self.rows, self.ld, self.group = int(rows), int(ld), group
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        nbytes = self.rows * self.ld * 4
+        with torch.cuda.device(device):
+            ptr = _ffi.c_p()
+            _ffi.call("sgc_symm_alloc", nbytes, ctypes.byref(ptr))
+            handle = ctypes.create_string_buffer(_ffi.IPC_HANDLE_BYTES)
+            _ffi.call("sgc_ipc_export", ptr, handle)
+            handles = [None] * self.world
+            dist.all_gather_object(handles, handle.raw, group=group)
+            self.ptrs, opened = [], []
+            for r in range(self.world):
+                if r == self.rank:
+                    self.ptrs.append(int(ptr.value))
+                    continue
+                peer = _ffi.c_p()
+                _ffi.call("sgc_ipc_open", ctypes.create_string_buffer(handles[r], _ffi.IPC_HANDLE_BYTES),
+                          ctypes.byref(peer))
+                self.ptrs.append(int(peer.value))
+                opened.append(int(peer.value))
+            self.tensor = torch.as_tensor(_DeviceMemory(ptr.value, (self.rows, self.ld)), device=device)
+        dist.barrier(group=group)          # nobody frees or writes before everyone has mapped
+        self._fin = weakref.finalize(self, _release_symm, int(ptr.value), opened)
+
+    def row_ptrs(self, row, peers_only):
+        """Device address of row `row` in every rank's copy (optionally without this rank's)."""
+        off = int(row) * self.ld * 4
+        return [p + off for r, p in enumerate(self.ptrs) if not (peers_only and r == self.rank)]
+
+    def close(self):
+        self.tensor = None
+        self._fin()
+
+
+class ShardedPropagator(object):
+    """Buffers + schedule for K-hop propagation on a ShardedGraph (see module docstring)."""
+
+    def __init__(self, sg, f, row_blocks=None, group=None, hop_fn=None, mode=None):
         self.sg, self.f, self.group = sg, int(f), group
         self.hop_fn = hop_fn or _cuda_hop
         g = sg.graph
         dev = g.device
+        self.mode = mode or ("exchange" if hop_fn is not None else default_mode(dev))
         self.ld = _pad8(self.f)
         n_all = sg.world * sg.n_pad
+        _, self.parts = partition_rows(sg.n_global, sg.world)
+        if self.mode == "push":
+            self.symm = [SymmetricBuffer(n_all, self.ld, dev, group) for _ in range(2)]
+            self.buf = [b.tensor for b in self.symm]
+            self._flag = torch.zeros(1, dtype=torch.float32, device=dev)
+            self.n_blocks, self.blk, self.blocks = 1, sg.n_pad, [g]
+            return
         self.buf = [torch.zeros((n_all, self.ld), dtype=torch.float32, device=dev) for _ in range(2)]
         self.n_blocks = max(1, min(int(row_blocks or default_row_blocks()), max(sg.n_pad, 1)))
         self.blk = (sg.n_pad + self.n_blocks - 1) // self.n_blocks
-        _, self.parts = partition_rows(sg.n_global, sg.world)
         # one sub-graph (views into the same CSR arrays) per row block of this rank
         self.blocks = []
         for r in range(self.n_blocks):
@@ -114,6 +196,41 @@ class ShardedPropagator(object):
         n_local = self.parts[rank][1] - self.parts[rank][0]
         return min(r * self.blk, n_local), min((r + 1) * self.blk, n_local)
 
+    # -- push mode -----------------------------------------------------------------------------
+    def _barrier(self):
+        """Stream-ordered rendezvous of all ranks: a one-element all-reduce enqueued behind the hop
+        kernel.  When it completes on a rank, every rank's preceding kernel -- and therefore every
+        NVLink store it issued into this rank's buffers -- has completed."""
+        if self.sg.world > 1:
+            dist.all_reduce(self._flag, group=self.group)
+
+    def _push_load(self, x_local):
+        sg = self.sg
+        if sg.n_local == 0:
+            self._barrier()
+            return
+        x_local = x_local if (x_local.dtype == torch.float32 and x_local.stride(1) == 1) else x_local.float().contiguous()
+        dsts = self.symm[0].row_ptrs(sg.row0, peers_only=False)
+        arr = (_ffi.c_p * len(dsts))(*dsts)
+        with torch.cuda.device(x_local.device):
+            _ffi.call("sgc_push_rows", x_local.data_ptr(), x_local.stride(0), sg.n_local, self.f, arr, len(dsts),
+                      self.ld, torch.cuda.current_stream().cuda_stream)
+        self._barrier()
+
+    def _push_propagate(self, degree):
+        sg = self.sg
+        for k in range(degree):
+            src, dst = self.buf[k % 2], self.symm[(k + 1) % 2]
+            last = (k == degree - 1)
+            if sg.n_local > 0:
+                peers = None if (last or sg.world == 1) else dst.row_ptrs(sg.row0, peers_only=True)
+                self.hop_fn(sg.graph, src[:, :self.f], dst.tensor[sg.row0:sg.row1, :self.f], peers)
+            # after the barrier: all rows of hop k are in place everywhere, and nobody still reads
+            # the buffer the next hop (or the next load) overwrites
+            self._barrier()
+        return self.buf[degree % 2][sg.row0:sg.row1, :self.f]
+
+    # -- exchange mode ---------------------------------------------------------------------------
     def _exchange_block(self, dst, r):
         """Send this rank's rows of block r (already written into dst) to every peer and receive
         theirs, each piece landing at its final position in dst."""
@@ -136,6 +253,8 @@ class ShardedPropagator(object):
         state the reference starts sgc_precompute from -- X fully resident)."""
         sg = self.sg
         assert tuple(x_local.shape) == (sg.n_local, self.f)
+        if self.mode == "push":
+            return self._push_load(x_local)
         self.buf[0][sg.row0:sg.row1, :self.f].copy_(x_local)
         works = []
         for r in range(self.n_blocks):
@@ -145,6 +264,8 @@ class ShardedPropagator(object):
 
     def propagate_resident(self, degree):
         """K hops starting from buf[0]; returns this rank's rows of S^K X as a [n_local, F] view."""
+        if self.mode == "push":
+            return self._push_propagate(degree)
         sg = self.sg
         pending = []
         for k in range(degree):
@@ -169,9 +290,29 @@ class ShardedPropagator(object):
         self.load(x_local)
         return self.propagate_resident(degree)
 
+    def rebind(self, sg):
+        """Reuse the buffers (and, in push mode, the peer mappings) for another ShardedGraph of the
+        same partition -- they are a per-shape resource like a communicator."""
+        assert (sg.world, sg.n_pad, sg.row0, sg.row1) == (self.sg.world, self.sg.n_pad, self.sg.row0, self.sg.row1)
+        self.sg = sg
+        if self.mode == "push":
+            self.blocks = [sg.graph]
+        return self
 
-def propagate_sharded(sg, x_local, degree, row_blocks=None, group=None, hop_fn=None):
-    return ShardedPropagator(sg, x_local.shape[1], row_blocks, group, hop_fn).propagate(x_local, degree).clone()
+    def close(self):
+        if self.mode == "push":
+            self.buf = []
+            for b in self.symm:
+                b.close()
+
+
+def propagate_sharded(sg, x_local, degree, row_blocks=None, group=None, hop_fn=None, mode=None):
+    prop = ShardedPropagator(sg, x_local.shape[1], row_blocks, group, hop_fn, mode)
+    out = prop.propagate(x_local, degree).clone()
+    if prop.mode == "push":
+        torch.cuda.synchronize(out.device)
+        prop.close()
+    return out
 
 
 # --------------------------------------------------------------------------------------------------
@@ -243,6 +384,7 @@ def bench(args, rank, world, dev, B):
     nnz = int(sum(int(t.item()) for t in nnz_all))
     from .propagate import default_chunk
     prop = ShardedPropagator(sg, f)
+    mode = prop.mode
     for r in range(prop.n_blocks):
         if prop.blocks[r] is not None:
             prop.blocks[r].plan(default_chunk())
@@ -286,7 +428,10 @@ def bench(args, rank, world, dev, B):
         sgl = shard_normalize(n, host["rp"].to(dev, non_blocking=True), host["col"].to(dev, non_blocking=True),
                               host["val"].to(dev, non_blocking=True))
         xl = host["x"].to(dev, non_blocking=True)
-        yl = ShardedPropagator(sgl, f).propagate(xl, k)
+        if mode == "push":
+            yl = prop.rebind(sgl).propagate(xl, k)      # symmetric buffers + peer mappings are reused
+        else:
+            yl = ShardedPropagator(sgl, f).propagate(xl, k)
         out_host.copy_(yl, non_blocking=True)
         torch.cuda.synchronize()
 
@@ -309,10 +454,15 @@ def bench(args, rank, world, dev, B):
             "metric": B["METRIC"], "value": value, "unit": B["UNIT"], "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": B["workload_config"](name, n, nnz, f, k, parallelism="row-sharded x%d; per-hop NVLink exchange (NCCL "
-                                           "send/recv groups) pipelined with the SpMM over %d row blocks; X "
-                                           "replicated at start, output sharded" % (world, prop.n_blocks),
-                                           normalise_ms=normalise_ms, rows_per_rank=n_pad),
+            "config": B["workload_config"](
+                name, n, nnz, f, k,
+                parallelism=("row-sharded x%d; exchange fused into the SpMM kernel: every output row is stored "
+                             "from the epilogue registers to all peers' next-hop operands over NVLink (CUDA IPC "
+                             "mapped), one tiny all-reduce as barrier per hop; X replicated at start, output sharded"
+                             % world) if mode == "push" else
+                            ("row-sharded x%d; per-hop NVLink exchange (NCCL send/recv groups) pipelined with the "
+                             "SpMM over %d row blocks; X replicated at start, output sharded" % (world, prop.n_blocks)),
+                dist_mode=mode, normalise_ms=normalise_ms, rows_per_rank=n_pad),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                          "kernel": "spmm_hop_kernel (per GPU; includes time waiting for the exchange)"},

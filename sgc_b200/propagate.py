@@ -63,8 +63,14 @@ def as_graph(adj):
     raise TypeError("adj must be an SgcGraph or a CUDA torch sparse tensor, got %r" % type(adj))
 
 
-def _hop_args(g, plan, x, ldx, y, ldy, f, partial, mean, std, std_mode, slab, hints):
+def _hop_args(g, plan, x, ldx, y, ldy, f, partial, mean, std, std_mode, slab, hints, peers=None):
     a = _ffi.HopArgs()
+    if peers:
+        if len(peers) > _ffi.MAX_PEERS:
+            raise ValueError("at most %d peers" % _ffi.MAX_PEERS)
+        a.n_peers = len(peers)
+        for i, ptr in enumerate(peers):
+            a.peer_y_d[i] = int(ptr)
     flags = 0
     if g.fused:
         flags |= _ffi.HOP_FUSED_NORM
@@ -101,9 +107,11 @@ def _partial(plan, f, dev):
     return torch.empty((plan.partial_rows, (f + 3) // 4 * 4), dtype=torch.float32, device=dev)
 
 
-def hop(adj, x, mean=None, std=None, chunk=None, slab=None, hints=None, std_mode=None, out=None):
+def hop(adj, x, mean=None, std=None, chunk=None, slab=None, hints=None, std_mode=None, out=None, peers=None):
     """One hop ``S @ x`` (torch.spmm(adj, x), utils.py:95).  Returns a new [n_rows, F] fp32
-    tensor.  With ``mean``/``std`` (fp32 [F]) the gathered operand is standardised on the fly."""
+    tensor.  With ``mean``/``std`` (fp32 [F]) the gathered operand is standardised on the fly.
+    ``peers``: device addresses of other GPUs' buffers (same row 0 and leading dimension as ``out``)
+    that receive every output row from the kernel's epilogue (row-sharded propagation, dist.py)."""
     g = as_graph(adj)
     dev = require_cuda(g.device)
     x = _check_features(g, x)
@@ -118,7 +126,7 @@ def hop(adj, x, mean=None, std=None, chunk=None, slab=None, hints=None, std_mode
         partial = _partial(plan, f, dev)
         a = _hop_args(g, plan, x.data_ptr(), x.stride(0), y.data_ptr(), y.stride(0), f, partial, mean, std,
                       std_mode or default_std_mode(), default_slab() if slab is None else slab,
-                      default_hints() if hints is None else hints)
+                      default_hints() if hints is None else hints, peers)
         _ffi.call("sgc_spmm_hop", plan.handle, _ffi.ctypes.byref(a), stream_ptr())
     return y
 

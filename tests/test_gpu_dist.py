@@ -19,7 +19,7 @@ def free_port():
         return s.getsockname()[1]
 
 
-def worker(rank, world, port, scale, f, k, slab_w, ret):
+def worker(rank, world, port, scale, f, k, slab_w, mode, ret):
     os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
     torch.cuda.set_device(rank)
     dev = torch.device("cuda", rank)
@@ -34,7 +34,7 @@ def worker(rank, world, port, scale, f, k, slab_w, ret):
         row0, row1 = parts[rank]
         rp, col, val = sd.local_rows_of((s["row_ptr"], s["col"], s["val"]), row0, row1)
         sg = sd.shard_normalize(n, rp, col, val)
-        y = sd.propagate_sharded(sg, x[row0:row1].contiguous(), k, row_blocks=slab_w)
+        y = sd.propagate_sharded(sg, x[row0:row1].contiguous(), k, row_blocks=slab_w, mode=mode)
         # single-GPU result on the same device
         full = sgc_b200.normalize_csr(n, s["row_ptr"], s["col"], s["val"])
         want, _ = sgc_b200.sgc_precompute(x, full, k)
@@ -47,7 +47,7 @@ def worker(rank, world, port, scale, f, k, slab_w, ret):
 
 def run(world, **kw):
     ret = mp.Manager().dict()
-    args = (world, free_port(), kw.get("scale", 0.02), kw.get("f", 100), kw.get("k", 3), kw.get("slab_w", 4), ret)
+    args = (world, free_port(), kw.get("scale", 0.02), kw.get("f", 100), kw.get("k", 3), kw.get("slab_w", 4), kw.get("mode", "push"), ret)
     mp.spawn(worker, args=args, nprocs=world, join=True)
     for rank in range(world):
         ok, same_struct, same_d, rows = ret[rank]
@@ -58,12 +58,60 @@ def run(world, **kw):
 def test_sharded_world1_bit_identical():
     if not torch.cuda.is_available():
         pytest.skip("no CUDA device")
-    run(1, f=100, k=3, slab_w=4)
-    run(1, f=602, k=2, slab_w=1)
+    run(1, f=100, k=3, slab_w=4, mode="exchange")
+    run(1, f=602, k=2, slab_w=1, mode="exchange")
+    run(1, f=100, k=3, mode="push")
+    run(1, f=602, k=2, mode="push")
 
 
 def test_sharded_world2_bit_identical():
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
-    run(2, f=100, k=3, slab_w=4)
-    run(2, f=130, k=2, slab_w=3)
+    run(2, f=100, k=3, slab_w=4, mode="exchange")
+    run(2, f=130, k=2, slab_w=3, mode="exchange")
+    run(2, f=100, k=3, mode="push")
+    run(2, f=130, k=2, mode="push")
+    run(2, f=602, k=2, mode="push")
+
+
+def test_hop_pushes_rows_to_peer_buffers():
+    """The fused exchange on ONE GPU: two extra local buffers stand in for the peers' mapped
+    operands; after the hop they must hold exactly the rows the kernel wrote locally (long rows
+    go through the fix-up kernel, which pushes too), and nothing else."""
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    import sgc_b200
+    from sgc_b200 import synth
+    dev = torch.device("cuda", 0)
+    s = synth.make_shape("reddit", device=dev, scale=0.02, seed=5)
+    n = s["n"]
+    g = sgc_b200.normalize_csr(n, s["row_ptr"], s["col"], s["val"])
+    for f in (100, 130, 602, 7):
+        ld = (f + 7) // 8 * 8
+        x = s["x"][:, :f].contiguous()
+        want = sgc_b200.hop(g, x, chunk=64)
+        bufs = [torch.full((n + 3, ld), -7.0, device=dev) for _ in range(3)]
+        own, peers = bufs[0], bufs[1:]
+        sgc_b200.hop(g, x, chunk=64, out=own[2:2 + n, :f], peers=[p[2:].data_ptr() for p in peers])
+        for b in bufs:
+            assert torch.equal(b[2:2 + n, :f], want)
+            assert bool((b[:2] == -7.0).all()) and bool((b[2 + n:] == -7.0).all()) and bool((b[:, f:] == -7.0).all())
+
+
+def test_push_rows_kernel():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    import ctypes
+    from sgc_b200 import _ffi
+    dev = torch.device("cuda", 0)
+    for f, ld_src in ((100, 100), (602, 602), (602, 608), (5, 8)):
+        rows, ld = 37, (f + 7) // 8 * 8
+        src = torch.randn((rows, ld_src), device=dev)
+        dst = [torch.full((rows + 2, ld), 3.0, device=dev) for _ in range(3)]
+        arr = (_ffi.c_p * 3)(*[d[1:].data_ptr() for d in dst])
+        _ffi.call("sgc_push_rows", src.data_ptr(), ld_src, rows, f, arr, 3, ld, torch.cuda.current_stream().cuda_stream)
+        for d in dst:
+            assert torch.equal(d[1:1 + rows, :f], src[:, :f])
+            assert bool((d[0] == 3.0).all()) and bool((d[-1] == 3.0).all())
+            if ld_src == f:
+                assert bool((d[:, f:] == 3.0).all())
