@@ -257,6 +257,9 @@ def run_own(args):
         _, standardise_ms = timed(lambda: sgc_b200.standardize_(x, mean32, std32))   # utils.py:119, exact, in place
     nnz = graph.nnz
     graph.plan(sgc_b200.propagate.default_chunk())
+    sval_ms = 0.0
+    if not sgc_b200.propagate.fused_norm():
+        _, sval_ms = timed(graph.values32)
 
     def step():
         # what utils.sgc_precompute times in the reference: K hops on (standardised) features
@@ -330,7 +333,10 @@ def run_own(args):
         "config": workload_config(name, n, nnz, f, k, normalise_ms=normalise_ms, col_stats_ms=stats_ms,
                                   standardise_inplace_ms=standardise_ms,
                                   chunk=sgc_b200.propagate.default_chunk(),
-                                  fused_into_hop=["D^-1/2 row/column scaling (S never materialised)"],
+                                  weights=("fp32((d_i*a_ij)*d_j) formed in the hop kernel (SGC_B200_FUSED_NORM=1)"
+                                           if sgc_b200.propagate.fused_norm() else
+                                           "fp32 S values written once by sgc_norm_build (%.3f ms, outside the timed "
+                                           "hops like the reference's normalisation), streamed by every hop" % sval_ms),
                                   timed_region="K hops on device-resident CSR + standardised X, as "
                                                "utils.py:93-96 times them; K1/K2/K3 + standardisation "
                                                "timed separately (above) and inside e2e"),

@@ -50,6 +50,10 @@ int32_t sgc_device_check(int32_t device);
 /* Number of kernels this library has launched in the calling process (bench.py gpu_launches). */
 int64_t sgc_launch_count(void);
 
+/* Sets the current device's L2 set-aside for persisting (evict_last) lines, clamped to the
+ * device maximum; the granted size is written to granted_out (may be NULL).  Process-wide. */
+int32_t sgc_l2_set_persisting_bytes(int64_t bytes, int64_t *granted_out);
+
 /* ---- generic device primitives ------------------------------------------------------------ */
 size_t  sgc_scan_workspace_bytes(int64_t n);
 /* In-place exclusive prefix sum of data_d[0..n) (int64). */
@@ -149,6 +153,19 @@ void    sgc_spmm_plan_destroy(sgc_plan_t *plan);
 /* Number of long-row chunk items (rows of the partial-sum buffer a hop needs). */
 int64_t sgc_spmm_plan_partial_rows(const sgc_plan_t *plan);
 
+/* Hot-column tagging (north_star (2): "L2 persistence hints keep the gathered X resident").  For
+ * operands far larger than L2 only the most frequently gathered rows of X are worth keeping:
+ * counts how often every column occurs in the plan's col array, chooses the count threshold above
+ * which at most `hot_rows` columns lie, and writes col_tagged_d[nnz] = col with bit 31 set on
+ * those columns.  Hops on this plan with hints bit 2 set then load tagged rows with an L2
+ * evict_last policy and all others with evict_first.  hot_rows <= 0 switches tagging off.
+ * SYNCHRONISES the stream (reads back a histogram).  col_tagged_d must outlive the plan.
+ * The plan's row_ptr/col may describe a row slice: counts are local to the slice, which is what
+ * this GPU's L2 sees. */
+size_t  sgc_spmm_hot_workspace_bytes(int64_t n_cols);
+int32_t sgc_spmm_plan_tag_hot(sgc_plan_t *plan, int64_t hot_rows, int32_t *col_tagged_d, void *ws_d,
+                              size_t ws_bytes, int64_t *n_hot_out, void *stream);
+
 #define SGC_MAX_PEERS        15   /* GPUs of one NVLink domain minus this one                       */
 
 #define SGC_HOP_FUSED_NORM   1u   /* weights = fp32((d_i*a_ij)*d_j) on the fly from aval_d + dinv_d */
@@ -172,7 +189,8 @@ typedef struct sgc_hop_args {
     int32_t       slab_floats; /* 0 = default                                                 */
     uint32_t      flags;
     int32_t       hints;       /* bit0: L2 evict_last policy on gathered x rows; bit1: evict_first on
-                                  the streamed col/value reads and the y stores                  */
+                                  the streamed col/value reads and the y stores; bit2: use the
+                                  plan's hot-column tags (sgc_spmm_plan_tag_hot) if it has them   */
     /* Row-sharded multi-GPU hop (K5): every output row is ALSO stored, from the registers of the
      * SpMM epilogue, to the same (row, column) offset of n_peers other buffers -- the peers'
      * copies of the gathered operand of the next hop, mapped into this process with

@@ -39,6 +39,7 @@ SIGNATURES = {
     "sgc_last_error": (ctypes.c_char_p, []),
     "sgc_device_check": (c_i32, [c_i32]),
     "sgc_launch_count": (c_i64, []),
+    "sgc_l2_set_persisting_bytes": (c_i32, [c_i64, ctypes.POINTER(c_i64)]),
     "sgc_scan_workspace_bytes": (c_sz, [c_i64]),
     "sgc_scan_exclusive_i64": (c_i32, [c_p, c_i64, c_p, c_sz, c_p]),
     "sgc_csr_check_canonical": (c_i32, [c_i64, c_i64, c_p, c_p, c_p, c_p]),
@@ -59,6 +60,8 @@ SIGNATURES = {
                                      ctypes.POINTER(c_p), c_p]),
     "sgc_spmm_plan_destroy": (None, [c_p]),
     "sgc_spmm_plan_partial_rows": (c_i64, [c_p]),
+    "sgc_spmm_hot_workspace_bytes": (c_sz, [c_i64]),
+    "sgc_spmm_plan_tag_hot": (c_i32, [c_p, c_i64, c_p, c_p, c_sz, ctypes.POINTER(c_i64), c_p]),
     "sgc_spmm_hop": (c_i32, [c_p, ctypes.POINTER(HopArgs), c_p]),
     "sgc_precompute": (c_i32, [c_p, ctypes.POINTER(HopArgs), c_i32, c_p, c_p, c_i64, c_p]),
     "sgc_symm_alloc": (c_i32, [c_sz, ctypes.POINTER(c_p)]),

@@ -161,6 +161,21 @@ int32_t sgc_device_check(int32_t device)
     return SGC_OK;
 }
 
+int32_t sgc_l2_set_persisting_bytes(int64_t bytes, int64_t *granted_out)
+{
+    int dev = 0;
+    SGC_CUDA_TRY(cudaGetDevice(&dev));
+    int max_bytes = 0;
+    SGC_CUDA_TRY(cudaDeviceGetAttribute(&max_bytes, cudaDevAttrMaxPersistingL2CacheSize, dev));
+    if (bytes < 0) bytes = 0;
+    if (bytes > (int64_t)max_bytes) bytes = max_bytes;
+    SGC_CUDA_TRY(cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, (size_t)bytes));
+    size_t got = 0;
+    SGC_CUDA_TRY(cudaDeviceGetLimit(&got, cudaLimitPersistingL2CacheSize));
+    if (granted_out) *granted_out = (int64_t)got;
+    return SGC_OK;
+}
+
 size_t sgc_scan_workspace_bytes(int64_t n) { return sgc::scan_workspace_bytes(n); }
 
 int32_t sgc_scan_exclusive_i64(int64_t *data_d, int64_t n, void *ws_d, size_t ws_bytes, void *stream)

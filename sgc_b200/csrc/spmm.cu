@@ -6,15 +6,15 @@
 
 namespace sgc {
 
-hop_launch_fn find_hop_kernel_v4(int g, int u, bool fused, int stdmode, bool peers);
-hop_launch_fn find_hop_kernel_v2(int g, int u, bool fused, int stdmode, bool peers);
-hop_launch_fn find_hop_kernel_v1(int g, int u, bool fused, int stdmode, bool peers);
+hop_launch_fn find_hop_kernel_v4(int g, int u, bool fused, int stdmode, bool peers, bool hot);
+hop_launch_fn find_hop_kernel_v2(int g, int u, bool fused, int stdmode, bool peers, bool hot);
+hop_launch_fn find_hop_kernel_v1(int g, int u, bool fused, int stdmode, bool peers, bool hot);
 
-hop_launch_fn find_hop_kernel(int g, int vec, int u, bool fused, int stdmode, bool peers)
+hop_launch_fn find_hop_kernel(int g, int vec, int u, bool fused, int stdmode, bool peers, bool hot)
 {
-    if (vec == 4) return find_hop_kernel_v4(g, u, fused, stdmode, peers);
-    if (vec == 2) return find_hop_kernel_v2(g, u, fused, stdmode, peers);
-    if (vec == 1) return find_hop_kernel_v1(g, u, fused, stdmode, peers);
+    if (vec == 4) return find_hop_kernel_v4(g, u, fused, stdmode, peers, hot);
+    if (vec == 2) return find_hop_kernel_v2(g, u, fused, stdmode, peers, hot);
+    if (vec == 1) return find_hop_kernel_v1(g, u, fused, stdmode, peers, hot);
     return nullptr;
 }
 
@@ -80,6 +80,42 @@ spmm_fixup_kernel(int64_t n_long_rows, const int32_t *__restrict__ lr_row,
         for (int j = 1; j < cnt; ++j) acc = __fadd_rn(acc, partial[(first + j) * ldp + c]);
         y[row * ldy + c] = acc;
         for (int pp = 0; pp < peers.n; ++pp) peers.y[pp][row * ldy + c] = acc;   // K5 push
+    }
+}
+
+// ---- hot-column tagging ----------------------------------------------------------------------------
+// When X is far larger than L2 (products / papers100M shapes) the hub rows are the only part of it
+// worth keeping in L2.  One-off, at plan time: count how often every column is gathered, pick the
+// count threshold above which at most `hot_rows` columns lie (a 64 Ki-bin histogram read back to
+// the host), and write a private copy of col with bit 31 set on those columns.
+constexpr int HOT_BINS = 65536;
+
+__global__ void __launch_bounds__(256)
+hot_count_kernel(int64_t nnz, const int32_t *__restrict__ col, uint32_t *__restrict__ cnt)
+{
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nnz;
+         i += (int64_t)gridDim.x * blockDim.x)
+        atomicAdd(cnt + col[i], 1u);
+}
+
+__global__ void __launch_bounds__(256)
+hot_hist_kernel(int64_t n_cols, const uint32_t *__restrict__ cnt, unsigned long long *__restrict__ hist)
+{
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_cols;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        const uint32_t c = cnt[i];
+        atomicAdd(hist + (c < HOT_BINS ? c : HOT_BINS - 1), 1ull);
+    }
+}
+
+__global__ void __launch_bounds__(256)
+hot_tag_kernel(int64_t nnz, const int32_t *__restrict__ col, const uint32_t *__restrict__ cnt,
+               uint32_t threshold, int32_t *__restrict__ col_tagged)
+{
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nnz;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        const int32_t c = col[i];
+        col_tagged[i] = (cnt[c] >= threshold) ? (c | (int32_t)0x80000000) : c;
     }
 }
 
@@ -183,7 +219,10 @@ static int32_t run_hop(const sgc_plan_impl *pl, const sgc_hop_args_t *a, const f
         }
     }
     const bool peers_on = push_peers && a->n_peers > 0;
-    hop_launch_fn fn = find_hop_kernel(g, vec, u, fused, stdmode, peers_on);
+    // hot-column tags are used when the plan has them, the caller asks (hints bit 2) and the
+    // variant exists (no fused standardisation)
+    const bool hot_on = pl->col_tagged != nullptr && (a->hints & 4) != 0 && stdmode == 0;
+    hop_launch_fn fn = find_hop_kernel(g, vec, u, fused, stdmode, peers_on, hot_on);
     if (!fn) {
         set_error("spmm_hop: kernel variant g=%d vec=%d u=%d fused=%d std=%d peers=%d not built", g, vec, u,
                   (int)fused, stdmode, (int)peers_on);
@@ -191,7 +230,7 @@ static int32_t run_hop(const sgc_plan_impl *pl, const sgc_hop_args_t *a, const f
     }
 
     HopDev p{};
-    p.row_ptr = pl->row_ptr; p.col = pl->col;
+    p.row_ptr = pl->row_ptr; p.col = hot_on ? pl->col_tagged : pl->col;
     p.aval = a->aval_d; p.dinv = a->dinv_d; p.sval = a->sval_d;
     p.dinv_rows = a->dinv_rows_d ? a->dinv_rows_d : a->dinv_d;
     p.x = x; p.ldx = ldx; p.y = y; p.ldy = ldy;
@@ -305,6 +344,65 @@ int32_t sgc_spmm_plan_create(int64_t n_rows, int64_t n_cols, int64_t nnz,
 }
 
 void sgc_spmm_plan_destroy(sgc_plan_t *plan) { delete plan; }
+
+size_t sgc_spmm_hot_workspace_bytes(int64_t n_cols)
+{
+    if (n_cols < 0) return 0;
+    return align256((size_t)n_cols * sizeof(uint32_t)) + align256((size_t)HOT_BINS * sizeof(unsigned long long)) + 256;
+}
+
+int32_t sgc_spmm_plan_tag_hot(sgc_plan_t *plan, int64_t hot_rows, int32_t *col_tagged_d, void *ws_d,
+                              size_t ws_bytes, int64_t *n_hot_out, void *stream)
+{
+    SGC_REQUIRE(plan, "plan_tag_hot: null plan");
+    sgc_plan_impl &P = plan->impl;
+    if (n_hot_out) *n_hot_out = 0;
+    if (hot_rows <= 0 || P.nnz == 0 || P.n_cols == 0) {          // switch tagging off
+        P.col_tagged = nullptr; P.n_hot_cols = 0; P.hot_threshold = 0;
+        return SGC_OK;
+    }
+    SGC_REQUIRE(col_tagged_d, "plan_tag_hot: col_tagged_d is null");
+    if (!ws_d || ws_bytes < sgc_spmm_hot_workspace_bytes(P.n_cols)) {
+        set_error("plan_tag_hot: workspace too small");
+        return SGC_ERR_WORKSPACE;
+    }
+    cudaStream_t s = as_stream(stream);
+    char *ws = reinterpret_cast<char *>(ws_d);
+    uint32_t *cnt = reinterpret_cast<uint32_t *>(ws);
+    const size_t cnt_bytes = align256((size_t)P.n_cols * sizeof(uint32_t));
+    unsigned long long *hist = reinterpret_cast<unsigned long long *>(ws + cnt_bytes);
+    SGC_CUDA_TRY(cudaMemsetAsync(ws, 0, cnt_bytes + (size_t)HOT_BINS * sizeof(unsigned long long), s));
+    hot_count_kernel<<<grid_for(ceil_div(P.nnz, 256), 8), 256, 0, s>>>(P.nnz, P.col, cnt);
+    SGC_LAUNCH_CHECK();
+    hot_hist_kernel<<<grid_for(ceil_div(P.n_cols, 256), 8), 256, 0, s>>>(P.n_cols, cnt, hist);
+    SGC_LAUNCH_CHECK();
+    unsigned long long *h = new (std::nothrow) unsigned long long[HOT_BINS];
+    SGC_REQUIRE(h, "plan_tag_hot: out of host memory");
+    cudaError_t e = cudaMemcpyAsync(h, hist, (size_t)HOT_BINS * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    if (e != cudaSuccess) { delete[] h; return cuda_fail(e, "plan_tag_hot readback", __FILE__, __LINE__); }
+    // smallest threshold (>= 2: a column gathered once gains nothing from staying in L2) whose
+    // column set fits the budget
+    unsigned long long above = 0;
+    int thr = HOT_BINS;             // "nothing is hot"
+    for (int b = HOT_BINS - 1; b >= 2; --b) {
+        if (above + h[b] > (unsigned long long)hot_rows) break;
+        above += h[b];
+        thr = b;
+    }
+    delete[] h;
+    if (thr >= HOT_BINS || above == 0) {
+        P.col_tagged = nullptr; P.n_hot_cols = 0; P.hot_threshold = 0;
+        return SGC_OK;
+    }
+    hot_tag_kernel<<<grid_for(ceil_div(P.nnz, 256), 8), 256, 0, s>>>(P.nnz, P.col, cnt, (uint32_t)thr, col_tagged_d);
+    SGC_LAUNCH_CHECK();
+    P.col_tagged = col_tagged_d;
+    P.n_hot_cols = (int64_t)above;
+    P.hot_threshold = thr;
+    if (n_hot_out) *n_hot_out = (int64_t)above;
+    return SGC_OK;
+}
 
 int64_t sgc_spmm_plan_partial_rows(const sgc_plan_t *plan) { return plan ? plan->impl.n_long_items : 0; }
 

@@ -68,12 +68,15 @@ struct sgc_plan_impl {
     const int32_t *lr_row;
     const int64_t *lr_first;
     const int32_t *lr_cnt;
+    const int32_t *col_tagged;   // col with bit 31 set on "hot" columns (sgc_spmm_plan_tag_hot), or null
+    int64_t n_hot_cols;
+    int32_t hot_threshold;
 };
 
 typedef int32_t (*hop_launch_fn)(const HopDev &, int64_t n_tasks, cudaStream_t);
 
 // Filled by the instantiation units (spmm_inst_*.cu).
-hop_launch_fn find_hop_kernel(int g, int vec, int u, bool fused, int stdmode, bool peers);
+hop_launch_fn find_hop_kernel(int g, int vec, int u, bool fused, int stdmode, bool peers, bool hot);
 
 #ifdef __CUDACC__
 
@@ -177,7 +180,10 @@ __device__ __forceinline__ float standardize(float x, float mu, float s)
     return x;
 }
 
-template <int G, int VEC, int U, bool FUSED, int STD, bool PEERS>
+// HOT: p.col carries a tag in bit 31 ("this column is among the most frequently gathered ones");
+// tagged rows of X are loaded with an L2 evict_last policy, all others with evict_first, which
+// pins the hub rows in L2 when X as a whole is far larger than L2.
+template <int G, int VEC, int U, bool FUSED, int STD, bool PEERS, bool HOT>
 __global__ void __launch_bounds__(HOP_THREADS, 5)
 spmm_hop_kernel(const HopDev p)
 {
@@ -194,7 +200,8 @@ spmm_hop_kernel(const HopDev p)
     const int64_t slab = task / per_slab;
     const int64_t t = task - slab * per_slab;
 
-    const uint64_t pol_x = l2_policy((p.hints & 1) ? 1 : 0);
+    const uint64_t pol_x = l2_policy(HOT ? 2 : ((p.hints & 1) ? 1 : 0));    // HOT: policy of untagged rows
+    const uint64_t pol_hot = l2_policy(1);
     const uint64_t pol_s = l2_policy((p.hints & 2) ? 2 : 0);
 
     bool valid = slab < p.n_slabs;
@@ -259,7 +266,7 @@ spmm_hop_kernel(const HopDev p)
             c = ld_stream_i32(p.col + idx, pol_s);
             if (FUSED) {
                 const double a = ld_stream_f64(p.aval + idx, pol_s);
-                const double dj = __ldg(p.dinv + c);
+                const double dj = __ldg(p.dinv + (HOT ? (c & 0x7fffffff) : c));
                 w = __double2float_rn(norm_value64(di, a, dj));
             } else {
                 w = ld_stream_f32(p.sval + idx, pol_s);
@@ -283,9 +290,10 @@ spmm_hop_kernel(const HopDev p)
             // predicated.  This keeps the UNR loads back to back in the instruction stream.
 #pragma unroll
             for (int jj = 0; jj < UNR; ++jj) {
-                const float *xr = p.x + (int64_t)cj[jj] * p.ldx;
+                const float *xr = p.x + (int64_t)(HOT ? (cj[jj] & 0x7fffffff) : cj[jj]) * p.ldx;
+                const uint64_t pol = (HOT && cj[jj] < 0) ? pol_hot : pol_x;
 #pragma unroll
-                for (int u = 0; u < U; ++u) xv[jj][u].load(xr + fo_ld[u], pol_x);
+                for (int u = 0; u < U; ++u) xv[jj][u].load(xr + fo_ld[u], pol);
             }
 #pragma unroll
             for (int jj = 0; jj < UNR; ++jj)
@@ -352,7 +360,7 @@ spmm_hop_kernel(const HopDev p)
     }
 }
 
-template <int G, int VEC, int U, bool FUSED, int STD, bool PEERS>
+template <int G, int VEC, int U, bool FUSED, int STD, bool PEERS, bool HOT>
 int32_t launch_hop(const HopDev &p, int64_t n_tasks, cudaStream_t s)
 {
     constexpr int GPW = 32 / G;
@@ -363,7 +371,7 @@ int32_t launch_hop(const HopDev &p, int64_t n_tasks, cudaStream_t s)
         set_error("spmm_hop: grid too large (%lld blocks)", (long long)blocks);
         return SGC_ERR_INVALID;
     }
-    spmm_hop_kernel<G, VEC, U, FUSED, STD, PEERS><<<(unsigned)blocks, HOP_THREADS, 0, s>>>(p);
+    spmm_hop_kernel<G, VEC, U, FUSED, STD, PEERS, HOT><<<(unsigned)blocks, HOP_THREADS, 0, s>>>(p);
     SGC_LAUNCH_CHECK();
     return SGC_OK;
 }

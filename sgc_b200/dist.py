@@ -167,6 +167,9 @@ class ShardedPropagator(object):
         self.hop_fn = hop_fn or _cuda_hop
         g = sg.graph
         dev = g.device
+        from .propagate import fused_norm
+        if g.fused and not fused_norm() and hop_fn is None:
+            g.values32()                      # materialise once so that row blocks share it
         self.mode = mode or ("exchange" if hop_fn is not None else default_mode(dev))
         self.ld = _pad8(self.f)
         n_all = sg.world * sg.n_pad

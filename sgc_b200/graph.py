@@ -171,10 +171,44 @@ class SgcGraph(object):
 _MATMULS = (torch.spmm, torch.sparse.mm, torch.mm, torch.matmul)
 
 
+L2_SLAB_BUDGET = 128 * 1024 * 1024      # same constant as spmm.cu: what one slab may occupy in L2
+
+
+def hot_budget_bytes():
+    """L2 bytes reserved for the most frequently gathered rows of X when X does not fit in L2
+    (SGC_B200_HOT_MB; 0 disables hot-column tagging)."""
+    import os
+    return int(float(os.environ.get("SGC_B200_HOT_MB", "64")) * 1024 * 1024)
+
+
 class _Plan(object):
     def __init__(self, handle, ws, partial_rows):
         self.handle, self.ws, self.partial_rows = handle, ws, partial_rows
         self._fin = weakref.finalize(self, _ffi.lib().sgc_spmm_plan_destroy, handle)
+        self.hot_key, self.col_tagged, self.n_hot = None, None, 0
+
+    def ensure_hot(self, graph, row_bytes):
+        """Tag the hub columns for an operand whose rows are `row_bytes` long, if not even the
+        narrowest feature slab of it fits in L2 (otherwise slab tiling keeps everything resident
+        and tags are switched off).  Cached per (row_bytes, budget)."""
+        budget = hot_budget_bytes()
+        need = budget > 0 and graph.n_cols * 32 * 4 > L2_SLAB_BUDGET and graph.nnz > 0
+        key = (int(row_bytes), budget) if need else None
+        if key == self.hot_key:
+            return
+        lib = _ffi.lib()
+        with torch.cuda.device(graph.device):
+            if not need:
+                _ffi.call("sgc_spmm_plan_tag_hot", self.handle, 0, None, None, 0, None, stream_ptr())
+                self.col_tagged, self.n_hot = None, 0
+            else:
+                ws = _ws(lib.sgc_spmm_hot_workspace_bytes(graph.n_cols), graph.device)
+                tagged = torch.empty(graph.nnz, dtype=torch.int32, device=graph.device)
+                n_hot = _ffi.c_i64(0)
+                _ffi.call("sgc_spmm_plan_tag_hot", self.handle, max(1, budget // int(row_bytes)), _ffi.ptr(tagged),
+                          _ffi.ptr(ws), ws.numel(), _ffi.ctypes.byref(n_hot), stream_ptr())
+                self.col_tagged, self.n_hot = (tagged if n_hot.value > 0 else None), int(n_hot.value)
+        self.hot_key = key
 
 
 # ---- K1 + K2: normalisation driver ------------------------------------------------------------------

@@ -26,7 +26,9 @@ def default_chunk():
 
 
 def default_hints():
-    return int(_ENV("SGC_B200_HINTS", "3"))
+    """bit0 evict_last on gathered rows (when the slab fits L2), bit1 evict_first on the CSR
+    stream and the output, bit2 use hot-column tags when X does not fit L2."""
+    return int(_ENV("SGC_B200_HINTS", "7"))
 
 
 def default_slab():
@@ -42,6 +44,15 @@ def default_std_mode():
                 1/std (<= 1 ulp per element).  Measured on B200 the gather touches every row of X
                 ~100 times, so per-element work inside it costs 3-13 ms -- see DESIGN.md."""
     return _ENV("SGC_B200_STD", "inplace")
+
+
+def fused_norm():
+    """SGC_B200_FUSED_NORM=1: the hop forms fp32((d_i*a_ij)*d_j) on the fly from the fp64 values of
+    A+I and D^-1/2, so S is never materialised (8 B + a D^-1/2 gather per stored entry and slab
+    pass).  Default 0: the same fp32 values are written once by sgc_norm_build (4 B per entry,
+    cached on the graph) and streamed by every hop -- bit-identical results, and measured 8-13 %
+    faster per hop on the Reddit shape (4.65 ms vs 5.1-5.4 ms), see DESIGN.md."""
+    return _ENV("SGC_B200_FUSED_NORM", "0") == "1"
 
 
 def _pad8(f):
@@ -65,6 +76,9 @@ def as_graph(adj):
 
 def _hop_args(g, plan, x, ldx, y, ldy, f, partial, mean, std, std_mode, slab, hints, peers=None):
     a = _ffi.HopArgs()
+    use_fused = g.fused and fused_norm()
+    if g.fused and not use_fused:
+        g.values32()                 # materialise S (fp32) once; cached on the graph
     if peers:
         if len(peers) > _ffi.MAX_PEERS:
             raise ValueError("at most %d peers" % _ffi.MAX_PEERS)
@@ -72,7 +86,7 @@ def _hop_args(g, plan, x, ldx, y, ldy, f, partial, mean, std, std_mode, slab, hi
         for i, ptr in enumerate(peers):
             a.peer_y_d[i] = int(ptr)
     flags = 0
-    if g.fused:
+    if use_fused:
         flags |= _ffi.HOP_FUSED_NORM
         a.aval_d, a.dinv_d, a.dinv_rows_d = _ffi.ptr(g.aval), _ffi.ptr(g.dinv), _ffi.ptr(g.dinv_rows)
     else:
@@ -123,6 +137,7 @@ def hop(adj, x, mean=None, std=None, chunk=None, slab=None, hints=None, std_mode
         if f == 0 or g.n_rows == 0:
             return y
         plan = g.plan(default_chunk() if chunk is None else chunk)
+        plan.ensure_hot(g, x.stride(0) * 4)
         partial = _partial(plan, f, dev)
         a = _hop_args(g, plan, x.data_ptr(), x.stride(0), y.data_ptr(), y.stride(0), f, partial, mean, std,
                       std_mode or default_std_mode(), default_slab() if slab is None else slab,
@@ -149,6 +164,7 @@ def propagate(adj, x, degree, mean=None, std=None, chunk=None, slab=None, hints=
         if f == 0 or n == 0:
             return y
         plan = g.plan(default_chunk() if chunk is None else chunk)
+        plan.ensure_hot(g, _pad8(f) * 4)
         partial = _partial(plan, f, dev)
         ld = _pad8(f)
         bufs = []

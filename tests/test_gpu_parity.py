@@ -207,6 +207,57 @@ def test_long_rows_split_and_exact_mode(dev):
         assert graph.plan(chunk).partial_rows > 0
 
 
+def test_hot_column_tags(dev, monkeypatch):
+    """Hot-column tagging (L2 pinning of hub rows for operands larger than L2) changes cache
+    policies only: results are bit-identical, the tagged set is exactly the columns whose gather
+    count reaches the chosen threshold, and it respects the row budget."""
+    import sgc_b200
+    from sgc_b200 import graph as graph_mod
+    s, graph = powerlaw_case(dev, scale=0.02, seed=13)
+    x = s["x"][:, :100].contiguous()
+    monkeypatch.setenv("SGC_B200_HOT_MB", "0")
+    base, _ = sgc_b200.sgc_precompute(x, graph, 2)
+    plan = graph.plan(sgc_b200.propagate.default_chunk())
+    assert plan.col_tagged is None
+    monkeypatch.setattr(graph_mod, "L2_SLAB_BUDGET", 1024)          # pretend nothing fits in L2
+    monkeypatch.setenv("SGC_B200_HOT_MB", "0.25")                   # 256 KiB / 416 B = 630 rows
+    got, _ = sgc_b200.sgc_precompute(x, graph, 2)
+    assert torch.equal(got, base)
+    assert plan.col_tagged is not None and 0 < plan.n_hot <= (256 * 1024) // 416
+    tagged = plan.col_tagged.cpu().numpy()
+    col = graph.col.cpu().numpy()
+    assert np.array_equal(tagged & 0x7fffffff, col)
+    counts = np.bincount(col, minlength=graph.n_cols)
+    hot_cols = np.unique(col[tagged < 0])
+    assert hot_cols.size == plan.n_hot
+    thr = counts[hot_cols].min()
+    assert np.array_equal(hot_cols, np.flatnonzero(counts >= thr))   # a pure count threshold
+    assert np.count_nonzero(counts >= thr - 1) > (256 * 1024) // 416 or thr == 2   # and the lowest that fits
+    # the fused-weights and peer-push variants take tags too
+    monkeypatch.setenv("SGC_B200_FUSED_NORM", "1")
+    got2, _ = sgc_b200.sgc_precompute(x, graph, 2)
+    assert torch.equal(got2, base)
+    monkeypatch.setenv("SGC_B200_HOT_MB", "0")
+    again, _ = sgc_b200.sgc_precompute(x, graph, 2)
+    assert plan.col_tagged is None and torch.equal(again, base)
+
+
+def test_fused_norm_mode_is_bit_identical(dev, monkeypatch):
+    """SGC_B200_FUSED_NORM=1 (weights formed in the kernel from fp64 A+I values and D^-1/2) and the
+    default (fp32 S values written once by sgc_norm_build) give the same bits, split rows included."""
+    import sgc_b200
+    s, graph = powerlaw_case(dev, scale=0.01, seed=9)
+    x = s["x"][:, :100].contiguous()
+    monkeypatch.setenv("SGC_B200_FUSED_NORM", "1")
+    assert graph.sval is None
+    a, _ = sgc_b200.sgc_precompute(x, graph, 2)
+    assert graph.sval is None                                      # nothing was materialised
+    monkeypatch.setenv("SGC_B200_FUSED_NORM", "0")
+    b, _ = sgc_b200.sgc_precompute(x, graph, 2)
+    assert graph.sval is not None
+    assert torch.equal(a, b)
+
+
 def test_fused_standardisation(dev):
     """First-hop standardisation fused into the gather == the oracle's hop on (x-mean)/std with the
     same fp32 statistics (DIV mode bit-exact; RCP mode within tolerance); statistics themselves
