@@ -190,7 +190,10 @@ typedef struct sgc_hop_args {
     uint32_t      flags;
     int32_t       hints;       /* bit0: L2 evict_last policy on gathered x rows; bit1: evict_first on
                                   the streamed col/value reads and the y stores; bit2: use the
-                                  plan's hot-column tags (sgc_spmm_plan_tag_hot) if it has them   */
+                                  plan's hot-column tags (sgc_spmm_plan_tag_hot) if it has them;
+                                  measurement aids for the multi-GPU hop: bit3 run the peer variant
+                                  but skip the pushes (results on peers are then stale), bit4 push
+                                  with per-lane stores instead of cp.async.bulk                  */
     /* Row-sharded multi-GPU hop (K5): every output row is ALSO stored, from the registers of the
      * SpMM epilogue, to the same (row, column) offset of n_peers other buffers -- the peers'
      * copies of the gathered operand of the next hop, mapped into this process with
@@ -199,6 +202,10 @@ typedef struct sgc_hop_args {
     int32_t       n_peers;
     int32_t       reserved_;
     float        *peer_y_d[SGC_MAX_PEERS];
+    /* Optional halo mask, one uint32 per row of this hop (n_rows entries): bit p set = peer p's
+     * shard gathers this row in the next hop, so it must be pushed to peer_y_d[p]; clear = peer p
+     * never reads it and the push is skipped.  NULL = push every row to every peer. */
+    const uint32_t *peer_mask_d;
 } sgc_hop_args_t;
 
 /* One hop Y = S X on `stream`. */
@@ -229,6 +236,11 @@ int32_t sgc_ipc_close(void *ptr_d);
 int32_t sgc_push_rows(const float *src_d, int64_t ld_src, int64_t rows, int32_t f,
                       float *const *dst_d /* host array of n_dst device pointers */, int32_t n_dst,
                       int64_t ld_dst, void *stream);
+
+/* Contiguous variant on the TMA unit: src_d[0..bytes) -> every dst_d[p][0..bytes) with
+ * cp.async.bulk (global -> shared -> global), tiles of tile_bytes, ctas_per_sm CTAs per SM. */
+int32_t sgc_push_bytes_bulk(const void *src_d, int64_t bytes, void *const *dst_d, int32_t n_dst,
+                            int32_t tile_bytes, int32_t ctas_per_sm, void *stream);
 
 #ifdef __cplusplus
 }

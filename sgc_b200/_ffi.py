@@ -30,6 +30,7 @@ class HopArgs(ctypes.Structure):
         ("mean_d", c_p), ("std_d", c_p),
         ("f", c_i32), ("slab_floats", c_i32), ("flags", c_u32), ("hints", c_i32),
         ("n_peers", c_i32), ("reserved_", c_i32), ("peer_y_d", c_p * 15),
+        ("peer_mask_d", c_p),
     ]
 
 
@@ -69,6 +70,7 @@ SIGNATURES = {
     "sgc_ipc_export": (c_i32, [c_p, c_p]),
     "sgc_ipc_open": (c_i32, [c_p, ctypes.POINTER(c_p)]),
     "sgc_ipc_close": (c_i32, [c_p]),
+    "sgc_push_bytes_bulk": (c_i32, [c_p, c_i64, ctypes.POINTER(c_p), c_i32, c_i32, c_i32, c_p]),
     "sgc_push_rows": (c_i32, [c_p, c_i64, c_i64, c_i32, ctypes.POINTER(c_p), c_i32, c_i64, c_p]),
 }
 

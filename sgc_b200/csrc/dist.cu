@@ -48,6 +48,49 @@ push_rows_kernel(const float *__restrict__ src, int64_t ld_src, int64_t rows, in
     }
 }
 
+// ---- bulk (TMA, non-tensor) variant: contiguous bytes -> every destination -----------------------
+// One elected thread per CTA streams tiles global -> shared (cp.async.bulk + mbarrier) and fans
+// each tile out to all destinations with cp.async.bulk shared -> global; two stages so that the
+// load of tile i+1 overlaps the stores of tile i.  The copies run on the TMA unit, not the LSU.
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__global__ void __launch_bounds__(32)
+push_bulk_kernel(const char *__restrict__ src, int64_t bytes, PushDst dst, int tile)
+{
+    extern __shared__ __align__(128) char stage[];          // 2 * tile
+    __shared__ __align__(8) uint64_t bar[2];
+    if (threadIdx.x != 0) return;
+    const uint32_t b0 = smem_u32(&bar[0]), b1 = smem_u32(&bar[1]);
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(b0));
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(b1));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    const int64_t n_tiles = (bytes + tile - 1) / tile;
+    int it = 0;
+    for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
+        const int st = it & 1;
+        const uint32_t phase = (uint32_t)(it >> 1) & 1u;
+        const uint32_t bar_a = st ? b1 : b0;
+        const uint32_t buf = smem_u32(stage + (size_t)st * tile);
+        // the stores issued two iterations ago have finished reading this stage
+        asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+        const int64_t off = t * (int64_t)tile;
+        const uint32_t size = (uint32_t)((bytes - off < tile) ? (bytes - off) : tile);
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar_a), "r"(size) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     :: "r"(buf), "l"(src + off), "r"(size), "r"(bar_a) : "memory");
+        uint32_t done = 0;
+        while (!done) {
+            asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+                         "selp.u32 %0, 1, 0, p;\n}" : "=r"(done) : "r"(bar_a), "r"(phase) : "memory");
+        }
+        for (int d = 0; d < dst.n; ++d)
+            asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+                         :: "l"(reinterpret_cast<char *>(dst.p[d]) + off), "r"(buf), "r"(size) : "memory");
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    }
+    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+
 }  // namespace sgc
 
 using namespace sgc;
@@ -129,6 +172,29 @@ int32_t sgc_push_rows(const float *src_d, int64_t ld_src, int64_t rows, int32_t 
         const int64_t work = rows * (int64_t)f;
         push_rows_kernel<1><<<grid_for(ceil_div(work, 256), 8), 256, 0, s>>>(src_d, ld_src, rows, f, d, ld_dst);
     }
+    SGC_LAUNCH_CHECK();
+    return SGC_OK;
+}
+
+int32_t sgc_push_bytes_bulk(const void *src_d, int64_t bytes, void *const *dst_d, int32_t n_dst,
+                            int32_t tile_bytes, int32_t ctas_per_sm, void *stream)
+{
+    SGC_REQUIRE(bytes >= 0 && bytes % 16 == 0, "push_bytes_bulk: byte count must be a multiple of 16");
+    SGC_REQUIRE(n_dst >= 0 && n_dst <= SGC_MAX_PEERS + 1, "push_bytes_bulk: n_dst out of range");
+    SGC_REQUIRE(tile_bytes >= 16 && tile_bytes % 16 == 0 && tile_bytes <= 100 * 1024, "push_bytes_bulk: bad tile size");
+    if (bytes == 0 || n_dst == 0) return SGC_OK;
+    SGC_REQUIRE(src_d && dst_d && (reinterpret_cast<uintptr_t>(src_d) & 15) == 0, "push_bytes_bulk: bad source");
+    PushDst d{};
+    d.n = n_dst;
+    for (int i = 0; i < n_dst; ++i) {
+        SGC_REQUIRE(dst_d[i] && (reinterpret_cast<uintptr_t>(dst_d[i]) & 15) == 0, "push_bytes_bulk: bad destination %d", i);
+        d.p[i] = reinterpret_cast<float *>(dst_d[i]);
+    }
+    if (ctas_per_sm < 1) ctas_per_sm = 4;
+    const size_t smem = 2 * (size_t)tile_bytes;
+    SGC_CUDA_TRY(cudaFuncSetAttribute(push_bulk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int grid = grid_for(ceil_div(bytes, tile_bytes), ctas_per_sm);
+    push_bulk_kernel<<<grid, 32, smem, as_stream(stream)>>>(reinterpret_cast<const char *>(src_d), bytes, d, tile_bytes);
     SGC_LAUNCH_CHECK();
     return SGC_OK;
 }

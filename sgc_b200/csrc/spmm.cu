@@ -61,7 +61,7 @@ plan_fill_kernel(int64_t n, const int64_t *__restrict__ row_ptr, int32_t chunk,
     }
 }
 
-struct PeerList { int32_t n; float *y[SGC_MAX_PEERS]; };
+struct PeerList { int32_t n; float *y[SGC_MAX_PEERS]; const uint32_t *mask; };
 
 // y[row] = partial[first] + partial[first+1] + ... in chunk order; one thread per
 // (long row, feature), consecutive threads on consecutive features.
@@ -79,7 +79,9 @@ spmm_fixup_kernel(int64_t n_long_rows, const int32_t *__restrict__ lr_row,
         float acc = partial[first * ldp + c];
         for (int j = 1; j < cnt; ++j) acc = __fadd_rn(acc, partial[(first + j) * ldp + c]);
         y[row * ldy + c] = acc;
-        for (int pp = 0; pp < peers.n; ++pp) peers.y[pp][row * ldy + c] = acc;   // K5 push
+        const uint32_t need = peers.mask ? peers.mask[row] : 0xffffffffu;
+        for (int pp = 0; pp < peers.n; ++pp)
+            if ((need >> pp) & 1u) peers.y[pp][row * ldy + c] = acc;             // K5 push
     }
 }
 
@@ -241,16 +243,20 @@ static int32_t run_hop(const sgc_plan_impl *pl, const sgc_hop_args_t *a, const f
     p.f = a->f; p.chunk = pl->chunk;
     p.n_slabs = (a->f + slab - 1) / slab;
     p.y_vec = y_vec;
-    p.hints = a->hints & 3;
+    p.hints = a->hints & (3 | 8 | 16);
     // keeping gathered rows with evict_last only helps when the slab can actually stay in L2
     if (!slab_fits_l2(pl->n_cols, slab < a->f ? slab : a->f)) p.hints &= ~1;
     SGC_REQUIRE(a->n_peers >= 0 && a->n_peers <= SGC_MAX_PEERS, "spmm_hop: n_peers out of range");
     p.n_peers = push_peers ? a->n_peers : 0;
     PeerList peers{};
     peers.n = p.n_peers;
+    p.peer_mask = peers.mask = (p.n_peers > 0) ? a->peer_mask_d : nullptr;
     for (int i = 0; i < p.n_peers; ++i) {
         SGC_REQUIRE(a->peer_y_d[i] != nullptr, "spmm_hop: peer_y_d[%d] is null", i);
         p.peer_y[i] = peers.y[i] = a->peer_y_d[i];
+        // the bulk-store path assumes the peers' copies are laid out like y (same alignment)
+        SGC_REQUIRE(y_vec != 4 || (reinterpret_cast<uintptr_t>(a->peer_y_d[i]) & 15) == 0,
+                    "spmm_hop: peer_y_d[%d] must be 16-byte aligned like y_d", i);
     }
     const int64_t n_tasks = (int64_t)p.n_slabs * (p.n_long_items + p.n_rows);
     int32_t rc = fn(p, n_tasks, s);

@@ -26,6 +26,7 @@
 namespace sgc {
 
 constexpr int HOP_THREADS = 128;
+__host__ __device__ constexpr int hop_tasks_per_warp(bool peers) { return peers ? 4 : 1; }
 
 struct HopDev {
     const int64_t *row_ptr;
@@ -54,6 +55,7 @@ struct HopDev {
     int32_t hints;       // bit0: L2 evict_last on gathered rows; bit1: evict_first on streams
     int32_t n_peers;     // K5: copies of y in other GPUs' memory that receive every output row
     float *peer_y[SGC_MAX_PEERS];
+    const uint32_t *peer_mask;   // per-row bit set of peers that need the row (null: all)
 };
 
 struct sgc_plan_impl {
@@ -184,7 +186,7 @@ __device__ __forceinline__ float standardize(float x, float mu, float s)
 // tagged rows of X are loaded with an L2 evict_last policy, all others with evict_first, which
 // pins the hub rows in L2 when X as a whole is far larger than L2.
 template <int G, int VEC, int U, bool FUSED, int STD, bool PEERS, bool HOT>
-__global__ void __launch_bounds__(HOP_THREADS, 5)
+__global__ void __launch_bounds__(HOP_THREADS, PEERS ? 7 : 5)
 spmm_hop_kernel(const HopDev p)
 {
     constexpr int GPW = 32 / G;                       // tasks per warp
@@ -192,17 +194,24 @@ spmm_hop_kernel(const HopDev p)
     constexpr int UNR = (U * VEC >= 8) ? 4 : 8;       // gathers in flight per lane
     static_assert(G % UNR == 0, "unroll must divide the group size");
 
+    // The peer variant walks TPW consecutive tasks per warp so that the NVLink pushes of one row
+    // drain while the next row is being gathered (see the epilogue).
+    constexpr int TPW = hop_tasks_per_warp(PEERS);
+
     const int lane = threadIdx.x & 31;
     const int gl = lane % G;
     const int64_t warp = (int64_t)blockIdx.x * (HOP_THREADS / 32) + (threadIdx.x >> 5);
-    const int64_t task = warp * GPW + lane / G;
     const int64_t per_slab = p.n_long_items + p.n_rows;
-    const int64_t slab = task / per_slab;
-    const int64_t t = task - slab * per_slab;
 
     const uint64_t pol_x = l2_policy(HOT ? 2 : ((p.hints & 1) ? 1 : 0));    // HOT: policy of untagged rows
     const uint64_t pol_hot = l2_policy(1);
     const uint64_t pol_s = l2_policy((p.hints & 2) ? 2 : 0);
+
+#pragma unroll 1
+    for (int it = 0; it < TPW; ++it) {
+    const int64_t task = (warp * TPW + it) * GPW + lane / G;
+    const int64_t slab = task / per_slab;
+    const int64_t t = task - slab * per_slab;
 
     bool valid = slab < p.n_slabs;
     int64_t row = 0, beg = 0, end = 0;
@@ -314,31 +323,77 @@ spmm_hop_kernel(const HopDev p)
         }
     }
 
-    if (!valid) return;
     const int sv = to_y ? (p.y_vec < VEC ? p.y_vec : VEC) : VEC;   // partial rows are padded and aligned
     const uint64_t pol_y = pol_s;
+    if (valid) {
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-        if (!act[u]) continue;
-        float *q = dst + fo[u];
-        if (VEC == 4 && sv == 4) {
-            st_hint_v4(q, acc[u], pol_y);
-        } else if (VEC >= 2 && sv >= 2) {
+        for (int u = 0; u < U; ++u) {
+            if (!act[u]) continue;
+            float *q = dst + fo[u];
+            if (VEC == 4 && sv == 4) {
+                st_hint_v4(q, acc[u], pol_y);
+            } else if (VEC >= 2 && sv >= 2) {
 #pragma unroll
-            for (int v = 0; v < VEC; v += 2)
-                if (fo[u] + v < p.f) st_hint_v2(q + v, &acc[u][v], pol_y);
-        } else {
+                for (int v = 0; v < VEC; v += 2)
+                    if (fo[u] + v < p.f) st_hint_v2(q + v, &acc[u][v], pol_y);
+            } else {
 #pragma unroll
-            for (int v = 0; v < VEC; ++v)
-                if (fo[u] + v < p.f) st_hint_v1(q + v, acc[u][v], pol_y);
+                for (int v = 0; v < VEC; ++v)
+                    if (fo[u] + v < p.f) st_hint_v1(q + v, acc[u][v], pol_y);
+            }
         }
     }
-    // K5: the same registers go to every peer's copy of the next hop's gathered operand.  The
-    // stores are fire-and-forget NVLink writes issued while other warps are still gathering, so
-    // the exchange overlaps the SpMM inside one kernel.
-    if (PEERS && to_y && p.n_peers > 0) {
+    if constexpr (PEERS) {
+    if (p.n_peers <= 0 || (p.hints & 8)) continue;     // hints bit 3: measurement aid, no push
+    // K5: every output row also goes to each peer's copy of the next hop's gathered operand, inside
+    // this kernel, while other warps are still gathering.
+    // Fast path (16-byte aligned output): the group's piece of the row is staged in shared memory in
+    // feature order and ONE lane hands it to the TMA unit -- a cp.async.bulk shared -> global per
+    // peer -- so the LSU never waits on NVLink and the fabric sees whole-row writes (measured 8 GPUs
+    // all-to-all: 640-680 GB/s per GPU against 544 GB/s for per-lane 16-byte stores).
+    if (p.y_vec == 4 && !(p.hints & 16)) {               // hints bit 4: force the per-lane store path
+        // Two staging buffers per warp: the bulk stores of task `it` keep reading buffer it&1 while
+        // task it+1 is gathered; before a buffer is overwritten, its issuing lane waits until at
+        // most the newer group is still reading (wait_group.read 1).
+        __shared__ __align__(128) float stage[HOP_THREADS / 32][2][32 * VEC * U];
+        float *mine = stage[threadIdx.x >> 5][it & 1] + (lane / G) * SW;
+        const bool push = valid && to_y;
+        if (gl == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+        __syncwarp();
+        if (push) {
+#pragma unroll
+            for (int u = 0; u < U; ++u)
+#pragma unroll
+                for (int v = 0; v < VEC; ++v) mine[(u * G + gl) * VEC + v] = act[u] ? acc[u][v] : 0.f;
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncwarp();
+        if (push && gl == 0) {
+            int nfl = p.f - f0;
+            nfl = nfl > SW ? SW : nfl;
+            const uint32_t bytes = (uint32_t)((nfl + 3) & ~3) * 4u;       // pad columns lie inside ldy
+            const uint32_t src = (uint32_t)__cvta_generic_to_shared(mine);
+            const int64_t off = row * p.ldy + f0;
+            const uint32_t need = p.peer_mask ? __ldg(p.peer_mask + row) : 0xffffffffu;
+            for (int pp = 0; pp < p.n_peers; ++pp)
+                if ((need >> pp) & 1u)
+                    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+                                 :: "l"(p.peer_y[pp] + off), "r"(src), "r"(bytes) : "memory");
+        }
+        // every leader commits one (possibly empty) group per task, so "1 pending" always means
+        // "the previous task's stores"
+        if (gl == 0) asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        if (it == TPW - 1 && gl == 0)
+            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // smem dies with the CTA
+        continue;
+    }
+    if (!valid) continue;
+    // Fallback for unaligned outputs: fire-and-forget per-lane stores from the registers.
+    if (to_y) {
         const int64_t off = row * p.ldy;
+        const uint32_t need = p.peer_mask ? __ldg(p.peer_mask + row) : 0xffffffffu;
         for (int pp = 0; pp < p.n_peers; ++pp) {
+            if (!((need >> pp) & 1u)) continue;
             float *base = p.peer_y[pp] + off;
 #pragma unroll
             for (int u = 0; u < U; ++u) {
@@ -358,13 +413,15 @@ spmm_hop_kernel(const HopDev p)
             }
         }
     }
+    }  // if constexpr (PEERS)
+    }  // task loop
 }
 
 template <int G, int VEC, int U, bool FUSED, int STD, bool PEERS, bool HOT>
 int32_t launch_hop(const HopDev &p, int64_t n_tasks, cudaStream_t s)
 {
     constexpr int GPW = 32 / G;
-    const int64_t warps = ceil_div(n_tasks, GPW);
+    const int64_t warps = ceil_div(n_tasks, GPW * hop_tasks_per_warp(PEERS));
     const int64_t blocks = ceil_div(warps, HOP_THREADS / 32);
     if (blocks <= 0) return SGC_OK;
     if (blocks > 0x7fffffffLL) {

@@ -93,9 +93,37 @@ def default_mode(device):
     return mode
 
 
-def _cuda_hop(graph, x, out, peers=None):
+def _cuda_hop(graph, x, out, peers=None, peer_mask=None):
     from .propagate import hop
-    hop(graph, x, out=out, peers=peers)
+    hop(graph, x, out=out, peers=peers, peer_mask=peer_mask)
+
+
+def halo_enabled():
+    """SGC_B200_DIST_HALO=0 pushes every row to every peer (plain all-gather semantics); default 1:
+    a row is pushed only to the peers whose shard actually gathers it."""
+    return os.environ.get("SGC_B200_DIST_HALO", "1") != "0"
+
+
+def needed_by_peers(sg, group=None):
+    """int32 [n_local]: bit p set = the p-th peer (ranks in ascending order, this rank left out)
+    stores at least one entry in column row0+i, i.e. gathers this rank's row i in every hop.
+    One pass over the local column indices plus one all-to-all of world*n_pad bytes."""
+    g, world, rank, n_pad = sg.graph, sg.world, sg.rank, sg.n_pad
+    dev = g.device
+    touch = torch.zeros(world * n_pad, dtype=torch.uint8, device=dev)
+    if g.nnz:
+        touch[g.col.long()] = 1
+    recv = torch.empty_like(touch)
+    dist.all_to_all_single(recv, touch, group=group)         # recv[q*n_pad + i] = rank q touches my row i
+    recv = recv.view(world, n_pad)[:, :sg.n_local].to(torch.int32)
+    mask = torch.zeros(sg.n_local, dtype=torch.int32, device=dev)
+    slot = 0
+    for q in range(world):
+        if q == rank:
+            continue
+        mask |= recv[q] << slot
+        slot += 1
+    return mask
 
 
 def _pad8(f):
@@ -175,10 +203,13 @@ class ShardedPropagator(object):
         n_all = sg.world * sg.n_pad
         _, self.parts = partition_rows(sg.n_global, sg.world)
         if self.mode == "push":
+            torch.cuda.empty_cache()          # the symmetric buffers come straight from cudaMalloc
             self.symm = [SymmetricBuffer(n_all, self.ld, dev, group) for _ in range(2)]
             self.buf = [b.tensor for b in self.symm]
             self._flag = torch.zeros(1, dtype=torch.float32, device=dev)
             self.n_blocks, self.blk, self.blocks = 1, sg.n_pad, [g]
+            self.peer_mask = needed_by_peers(sg, group) if (sg.world > 1 and halo_enabled()) else None
+            self.push_fraction = self._push_fraction()
             return
         self.buf = [torch.zeros((n_all, self.ld), dtype=torch.float32, device=dev) for _ in range(2)]
         self.n_blocks = max(1, min(int(row_blocks or default_row_blocks()), max(sg.n_pad, 1)))
@@ -200,6 +231,20 @@ class ShardedPropagator(object):
         return min(r * self.blk, n_local), min((r + 1) * self.blk, n_local)
 
     # -- push mode -----------------------------------------------------------------------------
+    def _push_fraction(self):
+        """Rows x peers actually pushed / (rows x peers), over all ranks (1.0 without halo masks)."""
+        sg = self.sg
+        if self.peer_mask is None or sg.world == 1:
+            return 1.0
+        bits = torch.zeros(1, dtype=torch.float64, device=self.peer_mask.device)
+        m = self.peer_mask
+        for slot in range(sg.world - 1):
+            bits += ((m >> slot) & 1).sum()
+        tot = torch.tensor([float(sg.n_local * (sg.world - 1))], dtype=torch.float64, device=m.device)
+        both = torch.cat([bits, tot])
+        dist.all_reduce(both, group=self.group)
+        return float(both[0].item() / max(both[1].item(), 1.0))
+
     def _barrier(self):
         """Stream-ordered rendezvous of all ranks: a one-element all-reduce enqueued behind the hop
         kernel.  When it completes on a rank, every rank's preceding kernel -- and therefore every
@@ -227,7 +272,8 @@ class ShardedPropagator(object):
             last = (k == degree - 1)
             if sg.n_local > 0:
                 peers = None if (last or sg.world == 1) else dst.row_ptrs(sg.row0, peers_only=True)
-                self.hop_fn(sg.graph, src[:, :self.f], dst.tensor[sg.row0:sg.row1, :self.f], peers)
+                self.hop_fn(sg.graph, src[:, :self.f], dst.tensor[sg.row0:sg.row1, :self.f], peers,
+                            None if peers is None else self.peer_mask)
             # after the barrier: all rows of hop k are in place everywhere, and nobody still reads
             # the buffer the next hop (or the next load) overwrites
             self._barrier()
@@ -297,9 +343,12 @@ class ShardedPropagator(object):
         """Reuse the buffers (and, in push mode, the peer mappings) for another ShardedGraph of the
         same partition -- they are a per-shape resource like a communicator."""
         assert (sg.world, sg.n_pad, sg.row0, sg.row1) == (self.sg.world, self.sg.n_pad, self.sg.row0, self.sg.row1)
+        changed = sg is not self.sg
         self.sg = sg
         if self.mode == "push":
             self.blocks = [sg.graph]
+            if changed and self.peer_mask is not None:
+                self.peer_mask = needed_by_peers(sg, self.group)     # the structure may differ
         return self
 
     def close(self):
@@ -326,73 +375,96 @@ def local_rows_of(graph_csr, row0, row1):
     return (row_ptr[row0:row1 + 1] - b).contiguous(), col[b:e].contiguous(), val[b:e].contiguous()
 
 
-def _single_gpu_reference(s, n, f, k, shape, dev):
+def _device_ms(fn, reps):
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(reps):
+        fn()
+    b.record()
+    torch.cuda.synchronize()
+    return a.elapsed_time(b) / reps
+
+
+def _single_gpu_reference(s, x, n, f, k, dev):
     """K hops of the whole graph on one GPU (rank 0), device-timed; for the strong-scaling ratio."""
-    from . import synth
     from .graph import normalize_csr
     from .propagate import propagate
     from .features import to_padded
     g = normalize_csr(n, s["row_ptr"], s["col"], s["val"])
-    x = to_padded(synth.gaussian_features(n, f, seed=1, scaled=shape["scaled"], device=dev))
-    for _ in range(2):
-        propagate(g, x, k)
+    xp = to_padded(x)
+    for _ in range(3):
+        propagate(g, xp, k)
     torch.cuda.synchronize()
-    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    reps = 3
-    a.record()
-    for _ in range(reps):
-        propagate(g, x, k)
-    b.record()
-    torch.cuda.synchronize()
-    ms = a.elapsed_time(b) / reps
+    ms = _device_ms(lambda: propagate(g, xp, k), 5)
     out = {"n_gpus": 1, "ms_per_step": ms, "value": k * g.nnz * f / (ms * 1e-3)}
-    del g, x
+    del g, xp
     torch.cuda.empty_cache()
     return out
 
 
-def bench(args, rank, world, dev, B):
-    """bench.py --gpus N (N > 1): row-sharded K-hop propagation of the products-shaped graph
-    (BASELINE configs[3]; strong scaling: the graph is fixed, rows are split over the ranks).
-    B: bench.py's module globals (helpers)."""
-    import json
-    import numpy as np
-    from . import _ffi, synth
-    from .features import padded_rows  # noqa: F401
-    name = args.workload if args.workload_given else "products"
+def bench_lambda():
+    """SGC_BENCH_LAMBDA: fraction of sampled edges forced into the source's own 1/8 block of nodes
+    (synth.powerlaw_graph `lam`; 0 = uniformly random neighbours, the default)."""
+    return float(os.environ.get("SGC_BENCH_LAMBDA", "0"))
+
+
+def _workload_inputs(name, rank, world, dev, want_single):
+    """This rank's rows of the named synthetic workload: raw CSR slice (global column ids) and the
+    feature rows the hops start from (Reddit shape: standardised as utils.py:119 does, with the
+    statistics of ALL rows).  Rank 0 also times the whole workload on its one GPU."""
+    from . import synth
+    from .features import col_stats, standardize_
     shape = synth.SHAPES[name]
     n, f, k = shape["n"], shape["f"], shape["k"]
     n_pad, parts = partition_rows(n, world)
     row0, row1 = parts[rank]
+    lam = bench_lambda()
     single = None
     if shape["symmetric"]:
-        s = synth.make_shape(name, device=dev, with_features=False)     # every rank builds the graph, keeps its rows
+        s = synth.make_shape(name, device=dev, with_features=False, lam=lam)     # every rank builds the graph, keeps its rows
         rp, col, val = local_rows_of((s["row_ptr"], s["col"], s["val"]), row0, row1)
-        if rank == 0 and os.environ.get("SGC_BENCH_SCALING_REF", "1") == "1":
-            single = _single_gpu_reference(s, n, f, k, shape, dev)
-        del s
+        if shape["scaled"]:
+            x = synth.gaussian_features(n, f, seed=1, scaled=True, device=dev)
+            mean, std = col_stats(x)
+            standardize_(x, mean, std)
+            x_local = x[row0:row1].clone()
+        else:
+            x = None
+            x_local = synth.gaussian_features(n, f, seed=1, scaled=False, row_range=(row0, row1), device=dev)
+        if rank == 0 and want_single:
+            if x is None:
+                x = synth.gaussian_features(n, f, seed=1, scaled=False, device=dev)
+            single = _single_gpu_reference(s, x, n, f, k, dev)
+        del s, x
     else:
-        s = synth.make_shape(name, device=dev, with_features=False, row_range=(row0, row1))
+        s = synth.make_shape(name, device=dev, with_features=False, row_range=(row0, row1), lam=lam)
         rp, col, val = s["row_ptr"], s["col"], s["val"]
+        x_local = synth.gaussian_features(n, f, seed=1, scaled=False, row_range=(row0, row1), device=dev)
+        del s
     torch.cuda.empty_cache()
-    x_local = synth.gaussian_features(n, f, seed=1, scaled=shape["scaled"], row_range=(row0, row1), device=dev)
+    return n, f, k, n_pad, rp, col, val, x_local, single
+
+
+def run_sharded_workload(name, args, rank, world, dev, B, with_e2e=True, want_single=True):
+    """Times K-hop row-sharded propagation of one named workload on `world` GPUs (strong scaling:
+    the graph is fixed, rows are split over the ranks).  Returns the measurements on rank 0."""
+    from . import _ffi
+    from .propagate import default_chunk
+    n, f, k, n_pad, rp, col, val, x_local, single = _workload_inputs(name, rank, world, dev, want_single)
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     sg = shard_normalize(n, rp, col, val)
     torch.cuda.synchronize()
     normalise_ms = (time.perf_counter() - t0) * 1e3
     nnz_local = torch.tensor([sg.graph.nnz], dtype=torch.int64, device=dev)
-    nnz_all = [torch.zeros_like(nnz_local) for _ in range(world)]
-    dist.all_gather(nnz_all, nnz_local)
-    nnz = int(sum(int(t.item()) for t in nnz_all))
-    from .propagate import default_chunk
+    dist.all_reduce(nnz_local)
+    nnz = int(nnz_local.item())
     prop = ShardedPropagator(sg, f)
     mode = prop.mode
-    for r in range(prop.n_blocks):
-        if prop.blocks[r] is not None:
-            prop.blocks[r].plan(default_chunk())
+    for blk in prop.blocks:
+        if blk is not None:
+            blk.plan(default_chunk())
 
-    ev = lambda: torch.cuda.Event(enable_timing=True)
     for _ in range(args.warmup):
         prop.load(x_local)
         prop.propagate_resident(k)
@@ -401,82 +473,121 @@ def bench(args, rank, world, dev, B):
     sampler = B["ClockSampler"](dev.index)
     sampler.start()
     launches0 = _ffi.launch_count()
-    torch.cuda.synchronize()
     total = 0.0
     for _ in range(args.steps):
         prop.load(x_local)         # untimed: X resident on every rank, the reference's starting state
         torch.cuda.synchronize()
         dist.barrier()
-        start, stop = ev(), ev()
+        start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         start.record()
-        y = prop.propagate_resident(k)
+        prop.propagate_resident(k)
         stop.record()
         torch.cuda.synchronize()
         total += start.elapsed_time(stop)
     dist.barrier()
-    torch.cuda.synchronize()
     ms = torch.tensor([total], dtype=torch.float64, device=dev)
     dist.all_reduce(ms, op=dist.ReduceOp.MAX)            # max over ranks, device-timed
     launches = _ffi.launch_count() - launches0
     clocks = sampler.stop()
     ms_per_step = float(ms.item()) / args.steps
-    value = k * nnz * f / (ms_per_step * 1e-3)
+    out = {"name": name, "n": n, "f": f, "k": k, "nnz": nnz, "n_pad": n_pad, "mode": mode,
+           "push_fraction": getattr(prop, "push_fraction", 1.0),
+           "n_blocks": prop.n_blocks, "normalise_ms": normalise_ms, "ms_per_step": ms_per_step,
+           "value": k * nnz * f / (ms_per_step * 1e-3), "launches": int(launches), "clocks": clocks,
+           "single": single, "e2e": None}
+    if with_e2e:
+        # end to end: this rank's shard from pinned host memory and back
+        host = {"rp": rp.cpu().pin_memory(), "col": col.cpu().pin_memory(), "val": val.cpu().pin_memory(),
+                "x": x_local.cpu().pin_memory()}
+        out_host = torch.empty((sg.n_local, f), dtype=torch.float32).pin_memory()
 
-    # end to end: this rank's shard from pinned host memory and back
-    host = {"rp": rp.cpu().pin_memory(), "col": col.cpu().pin_memory(), "val": val.cpu().pin_memory(),
-            "x": x_local.cpu().pin_memory()}
-    out_host = torch.empty((sg.n_local, f), dtype=torch.float32).pin_memory()
+        def e2e_step():
+            sgl = shard_normalize(n, host["rp"].to(dev, non_blocking=True), host["col"].to(dev, non_blocking=True),
+                                  host["val"].to(dev, non_blocking=True))
+            xl = host["x"].to(dev, non_blocking=True)
+            if mode == "push":
+                yl = prop.rebind(sgl).propagate(xl, k)      # symmetric buffers + peer mappings are reused
+            else:
+                yl = ShardedPropagator(sgl, f).propagate(xl, k)
+            out_host.copy_(yl, non_blocking=True)
+            torch.cuda.synchronize()
 
-    def e2e_step():
-        sgl = shard_normalize(n, host["rp"].to(dev, non_blocking=True), host["col"].to(dev, non_blocking=True),
-                              host["val"].to(dev, non_blocking=True))
-        xl = host["x"].to(dev, non_blocking=True)
-        if mode == "push":
-            yl = prop.rebind(sgl).propagate(xl, k)      # symmetric buffers + peer mappings are reused
-        else:
-            yl = ShardedPropagator(sgl, f).propagate(xl, k)
-        out_host.copy_(yl, non_blocking=True)
-        torch.cuda.synchronize()
-
-    e2e_step()
-    dist.barrier()
-    e2e_steps = max(2, min(args.steps, 3))
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
         e2e_step()
-    dist.barrier()
-    e2e_s = torch.tensor([(time.perf_counter() - t0) / e2e_steps], dtype=torch.float64, device=dev)
-    dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
-    h2d = torch.tensor([sum(t.numel() * t.element_size() for t in host.values())], dtype=torch.int64, device=dev)
-    dist.all_reduce(h2d)
+        dist.barrier()
+        e2e_steps = max(2, min(args.steps, 3))
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            e2e_step()
+        dist.barrier()
+        e2e_s = torch.tensor([(time.perf_counter() - t0) / e2e_steps], dtype=torch.float64, device=dev)
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+        h2d = torch.tensor([sum(t.numel() * t.element_size() for t in host.values())], dtype=torch.int64, device=dev)
+        dist.all_reduce(h2d)
+        out["e2e"] = {"value": k * nnz * f / float(e2e_s.item()), "unit": B["UNIT"],
+                      "h2d_bytes_per_step": int(h2d.item()), "d2h_bytes_per_step": int(n * f * 4),
+                      "ms_per_step": float(e2e_s.item()) * 1e3}
+        del host, out_host
+    prop.close()
+    del prop, sg
+    torch.cuda.empty_cache()
+    return out
+
+
+def _parallelism_text(r, world):
+    if r["mode"] == "push":
+        return ("row-sharded x%d; exchange fused into the SpMM kernel: every output row is staged in shared memory "
+                "and written by cp.async.bulk to all peers' next-hop operands over NVLink (CUDA-IPC mapped), one "
+                "1-element all-reduce as barrier per hop; a row goes only to the peers whose shard gathers it "
+                "(%.1f%% of rows x peers here); X replicated at start, output sharded"
+                % (world, 100.0 * r["push_fraction"]))
+    return ("row-sharded x%d; per-hop NVLink exchange (NCCL send/recv groups) pipelined with the SpMM over %d row "
+            "blocks; X replicated at start, output sharded" % (world, r["n_blocks"]))
+
+
+def bench(args, rank, world, dev, B):
+    """bench.py --gpus N (N > 1): the SAME workload as N = 1 (Reddit-shaped, BASELINE configs[2]) row-sharded
+    over the N GPUs, so that value(N) / value(1) is a strong-scaling ratio; by default the line also
+    carries the products-shaped workload (BASELINE configs[3], the config north_star names for the
+    1/2/4/8-GPU series) with its own single-GPU reference (SGC_BENCH_EXTRA="" to skip).
+    B: bench.py's module globals (helpers)."""
+    import json
+    name = args.workload
+    r = run_sharded_workload(name, args, rank, world, dev, B,
+                             with_e2e=(name != "papers100m" or os.environ.get("SGC_BENCH_PAPERS_E2E") == "1"))
+    extras = {}
+    extra_names = os.environ.get("SGC_BENCH_EXTRA", "products" if not args.workload_given else "")
+    for other in [e for e in extra_names.split(",") if e and e != name]:
+        try:
+            x = run_sharded_workload(other, args, rank, world, dev, B, with_e2e=False)
+            extras[other] = {"workload": B["workload_config"](other, x["n"], x["nnz"], x["f"], x["k"])["workload"],
+                             "n_gpus": world, "value": x["value"], "unit": B["UNIT"], "ms_per_step": x["ms_per_step"],
+                             "nnz_S": x["nnz"], "dist_mode": x["mode"], "single_gpu_same_workload": x["single"],
+                             "strong_scaling_efficiency": (x["value"] / (world * x["single"]["value"])
+                                                           if x["single"] else None)}
+        except Exception as exc:            # an optional extra must never cost the primary line
+            extras[other] = {"error": repr(exc)[:300]}
     if rank == 0:
+        n, f, k, nnz = r["n"], r["f"], r["k"], r["nnz"]
         peak, peak_src = B["peaks"]()
         b_hop = B["hop_bytes"](n, nnz, f)
-        achieved = k * b_hop / world / (ms_per_step * 1e-3) / 1e9      # per-GPU algorithmic GB/s
+        achieved = k * b_hop / world / (r["ms_per_step"] * 1e-3) / 1e9      # per-GPU algorithmic GB/s
         line = {
-            "metric": B["METRIC"], "value": value, "unit": B["UNIT"], "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
+            "metric": B["METRIC"], "value": r["value"], "unit": B["UNIT"], "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": B["workload_config"](
-                name, n, nnz, f, k,
-                parallelism=("row-sharded x%d; exchange fused into the SpMM kernel: every output row is stored "
-                             "from the epilogue registers to all peers' next-hop operands over NVLink (CUDA IPC "
-                             "mapped), one tiny all-reduce as barrier per hop; X replicated at start, output sharded"
-                             % world) if mode == "push" else
-                            ("row-sharded x%d; per-hop NVLink exchange (NCCL send/recv groups) pipelined with the "
-                             "SpMM over %d row blocks; X replicated at start, output sharded" % (world, prop.n_blocks)),
-                dist_mode=mode, normalise_ms=normalise_ms, rows_per_rank=n_pad),
+            "config": B["workload_config"](name, n, nnz, f, k, parallelism=_parallelism_text(r, world),
+                                           dist_mode=r["mode"], normalise_ms=r["normalise_ms"],
+                                           partition_locality_lambda=bench_lambda(),
+                                           pushed_rows_x_peers_fraction=r["push_fraction"],
+                                           rows_per_rank=r["n_pad"]),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                         "kernel": "spmm_hop_kernel (per GPU; includes time waiting for the exchange)"},
-            "cpu_baseline": None,
-            "e2e": {"value": k * nnz * f / float(e2e_s.item()), "unit": B["UNIT"],
-                    "h2d_bytes_per_step": int(h2d.item()), "d2h_bytes_per_step": int(n * f * 4),
-                    "ms_per_step": float(e2e_s.item()) * 1e3},
-            "gpu_launches": int(launches), "clocks": clocks,
+                         "kernel": "spmm_hop_kernel (per GPU; includes the fused NVLink pushes and the barrier)"},
+            "cpu_baseline": None, "e2e": r["e2e"], "gpu_launches": r["launches"], "clocks": r["clocks"],
             # the same workload on ONE GPU of this box, measured by rank 0 in this run, so that the
             # strong-scaling efficiency value / (n_gpus * single.value) can be read off this line
-            "single_gpu_same_workload": single,
+            "single_gpu_same_workload": r["single"],
+            "other_workloads": extras,
         }
         print(json.dumps(line), flush=True)
     dist.barrier()

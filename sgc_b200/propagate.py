@@ -74,7 +74,7 @@ def as_graph(adj):
     raise TypeError("adj must be an SgcGraph or a CUDA torch sparse tensor, got %r" % type(adj))
 
 
-def _hop_args(g, plan, x, ldx, y, ldy, f, partial, mean, std, std_mode, slab, hints, peers=None):
+def _hop_args(g, plan, x, ldx, y, ldy, f, partial, mean, std, std_mode, slab, hints, peers=None, peer_mask=None):
     a = _ffi.HopArgs()
     use_fused = g.fused and fused_norm()
     if g.fused and not use_fused:
@@ -85,6 +85,8 @@ def _hop_args(g, plan, x, ldx, y, ldy, f, partial, mean, std, std_mode, slab, hi
         a.n_peers = len(peers)
         for i, ptr in enumerate(peers):
             a.peer_y_d[i] = int(ptr)
+        if peer_mask is not None:
+            a.peer_mask_d = _ffi.ptr(peer_mask)
     flags = 0
     if use_fused:
         flags |= _ffi.HOP_FUSED_NORM
@@ -121,11 +123,13 @@ def _partial(plan, f, dev):
     return torch.empty((plan.partial_rows, (f + 3) // 4 * 4), dtype=torch.float32, device=dev)
 
 
-def hop(adj, x, mean=None, std=None, chunk=None, slab=None, hints=None, std_mode=None, out=None, peers=None):
+def hop(adj, x, mean=None, std=None, chunk=None, slab=None, hints=None, std_mode=None, out=None, peers=None,
+        peer_mask=None):
     """One hop ``S @ x`` (torch.spmm(adj, x), utils.py:95).  Returns a new [n_rows, F] fp32
     tensor.  With ``mean``/``std`` (fp32 [F]) the gathered operand is standardised on the fly.
     ``peers``: device addresses of other GPUs' buffers (same row 0 and leading dimension as ``out``)
-    that receive every output row from the kernel's epilogue (row-sharded propagation, dist.py)."""
+    that receive every output row from the kernel's epilogue (row-sharded propagation, dist.py);
+    ``peer_mask`` (int32/uint32 [n_rows], optional): bit p set = row must go to peers[p]."""
     g = as_graph(adj)
     dev = require_cuda(g.device)
     x = _check_features(g, x)
@@ -141,7 +145,7 @@ def hop(adj, x, mean=None, std=None, chunk=None, slab=None, hints=None, std_mode
         partial = _partial(plan, f, dev)
         a = _hop_args(g, plan, x.data_ptr(), x.stride(0), y.data_ptr(), y.stride(0), f, partial, mean, std,
                       std_mode or default_std_mode(), default_slab() if slab is None else slab,
-                      default_hints() if hints is None else hints, peers)
+                      default_hints() if hints is None else hints, peers, peer_mask)
         _ffi.call("sgc_spmm_hop", plan.handle, _ffi.ctypes.byref(a), stream_ptr())
     return y
 

@@ -57,7 +57,7 @@ def test_hop_args_layout_matches_c(built, tmp_path):
         "int main(void){printf(\"%zu\", sizeof(sgc_hop_args_t));\n"
         + "".join('printf(" %%zu", offsetof(sgc_hop_args_t, %s));\n' % f for f in
                   ["aval_d", "dinv_d", "dinv_rows_d", "sval_d", "x_d", "ldx", "y_d", "ldy", "partial_d", "ldp", "mean_d",
-                   "std_d", "f", "slab_floats", "flags", "hints", "n_peers", "reserved_", "peer_y_d"])
+                   "std_d", "f", "slab_floats", "flags", "hints", "n_peers", "reserved_", "peer_y_d", "peer_mask_d"])
         + "return 0;}\n")
     exe = tmp_path / "layout"
     subprocess.check_call(["gcc", "-I", os.path.join(REPO, "include"), str(src), "-o", str(exe)])

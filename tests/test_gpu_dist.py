@@ -19,7 +19,7 @@ def free_port():
         return s.getsockname()[1]
 
 
-def worker(rank, world, port, scale, f, k, slab_w, mode, ret):
+def worker(rank, world, port, scale, f, k, slab_w, mode, lam, ret):
     os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
     torch.cuda.set_device(rank)
     dev = torch.device("cuda", rank)
@@ -27,7 +27,7 @@ def worker(rank, world, port, scale, f, k, slab_w, mode, ret):
     try:
         import sgc_b200
         from sgc_b200 import dist as sd, synth
-        s = synth.make_shape("reddit", device=dev, scale=scale, seed=11)
+        s = synth.make_shape("reddit", device=dev, scale=scale, seed=11, lam=lam)
         n = s["n"]
         x = s["x"][:, :f].contiguous()
         n_pad, parts = sd.partition_rows(n, world)
@@ -47,7 +47,8 @@ def worker(rank, world, port, scale, f, k, slab_w, mode, ret):
 
 def run(world, **kw):
     ret = mp.Manager().dict()
-    args = (world, free_port(), kw.get("scale", 0.02), kw.get("f", 100), kw.get("k", 3), kw.get("slab_w", 4), kw.get("mode", "push"), ret)
+    args = (world, free_port(), kw.get("scale", 0.02), kw.get("f", 100), kw.get("k", 3), kw.get("slab_w", 4), kw.get("mode", "push"),
+            kw.get("lam", 0.0), ret)
     mp.spawn(worker, args=args, nprocs=world, join=True)
     for rank in range(world):
         ok, same_struct, same_d, rows = ret[rank]
@@ -72,6 +73,7 @@ def test_sharded_world2_bit_identical():
     run(2, f=100, k=3, mode="push")
     run(2, f=130, k=2, mode="push")
     run(2, f=602, k=2, mode="push")
+    run(2, f=100, k=3, mode="push", lam=0.95)      # partition locality: many rows no peer needs
 
 
 def test_hop_pushes_rows_to_peer_buffers():
@@ -95,7 +97,26 @@ def test_hop_pushes_rows_to_peer_buffers():
         sgc_b200.hop(g, x, chunk=64, out=own[2:2 + n, :f], peers=[p[2:].data_ptr() for p in peers])
         for b in bufs:
             assert torch.equal(b[2:2 + n, :f], want)
-            assert bool((b[:2] == -7.0).all()) and bool((b[2 + n:] == -7.0).all()) and bool((b[:, f:] == -7.0).all())
+            assert bool((b[:2] == -7.0).all()) and bool((b[2 + n:] == -7.0).all())
+            pad = b[2:2 + n, f:]                  # pad columns: untouched, or zero-filled by the bulk store
+            assert bool(((pad == -7.0) | (pad == 0.0)).all())
+        # halo mask: a row reaches peer p only if bit p of its mask is set
+        mask = torch.randint(0, 4, (n,), dtype=torch.int32, device=dev)
+        bufs = [torch.full((n + 3, ld), -7.0, device=dev) for _ in range(3)]
+        sgc_b200.hop(g, x, chunk=64, out=bufs[0][2:2 + n, :f], peers=[p[2:].data_ptr() for p in bufs[1:]],
+                     peer_mask=mask)
+        assert torch.equal(bufs[0][2:2 + n, :f], want)
+        for slot, b in enumerate(bufs[1:]):
+            sent = ((mask >> slot) & 1).bool()
+            assert torch.equal(b[2:2 + n, :f][sent], want[sent])
+            assert bool((b[2:2 + n][~sent] == -7.0).all())
+        # unaligned output (odd leading dimension): the per-lane store fallback
+        ldu = f + 1 if (f + 1) % 2 else f + 2
+        bufs = [torch.full((n + 3, ldu), -7.0, device=dev) for _ in range(3)]
+        sgc_b200.hop(g, x, chunk=64, out=bufs[0][1:1 + n, :f], peers=[p[1:].data_ptr() for p in bufs[1:]])
+        for b in bufs:
+            assert torch.equal(b[1:1 + n, :f], want)
+            assert bool((b[:1] == -7.0).all()) and bool((b[1 + n:] == -7.0).all()) and bool((b[:, f:] == -7.0).all())
 
 
 def test_push_rows_kernel():
