@@ -326,6 +326,17 @@ def run_own(args):
                "sample": "rows [0,%d) of one hop (%d of %d stored entries), torch.spmm fp32 on CPU, median of 3 (%.2f s each)"
                          % (rows, sample_nnz, nnz, secs)}
 
+    # ---- the other single-GPU-sized BASELINE config, for the 1/2/4/8-GPU series (not the headline) ----
+    others = {}
+    extra_names = os.environ.get("SGC_BENCH_EXTRA", "products" if not args.workload_given else "")
+    del graph, x, y, ybuf, s
+    torch.cuda.empty_cache()
+    for other in [e for e in extra_names.split(",") if e and e != name]:
+        try:
+            others[other] = single_gpu_extra(other, dev, peak)
+        except Exception as exc:        # an optional extra must never cost the primary line
+            others[other] = {"error": repr(exc)[:300]}
+
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
@@ -341,8 +352,37 @@ def run_own(args):
                                                "utils.py:93-96 times them; K1/K2/K3 + standardisation "
                                                "timed separately (above) and inside e2e"),
         "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+        "other_workloads": others,
     }
     print(json.dumps(line))
+
+
+def single_gpu_extra(name, dev, peak):
+    """K hops of another named workload on this one GPU (device-timed, 3 warm-ups + 5 steps)."""
+    import sgc_b200
+    s = make_workload(name, dev)
+    n, f, k = s["n"], s["f"], s["k"]
+    graph = sgc_b200.normalize_csr(n, s["row_ptr"], s["col"], s["val"])
+    x = sgc_b200.to_padded(s["x"])
+    del s
+    for _ in range(3):
+        sgc_b200.propagate.propagate(graph, x, k)
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(5):
+        sgc_b200.propagate.propagate(graph, x, k)
+    b.record()
+    torch.cuda.synchronize()
+    ms = a.elapsed_time(b) / 5
+    nnz = graph.nnz
+    achieved = k * hop_bytes(n, nnz, f) / (ms * 1e-3) / 1e9
+    out = {"workload": workload_config(name, n, nnz, f, k)["workload"], "n_gpus": 1, "value": k * nnz * f / (ms * 1e-3),
+           "unit": UNIT, "ms_per_step": ms, "nnz_S": nnz,
+           "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak}}
+    del graph, x
+    torch.cuda.empty_cache()
+    return out
 
 
 def run_e2e(args, s, name, k, nnz_s, dev):

@@ -269,6 +269,42 @@ static int32_t run_hop(const sgc_plan_impl *pl, const sgc_hop_args_t *a, const f
     return SGC_OK;
 }
 
+// When the feature width is not a multiple of the slab and the remainder is narrow (at most half a
+// slab), the last slab would run with most lanes of every group idle (e.g. 152 columns = one
+// 128-float slab + 24 columns on 32-lane groups).  The remainder is then a second launch on the
+// shifted column range with the narrowest group that covers it (24 columns -> 8 lanes, 4 rows per
+// warp).  Columns are independent, so results are unchanged.
+static int32_t run_hop_auto(const sgc_plan_impl *pl, const sgc_hop_args_t *a, const float *x,
+                            int64_t ldx, float *y, int64_t ldy, uint32_t flags, bool push_peers,
+                            cudaStream_t s)
+{
+    if (a->slab_floats == 0 && x && y && a->f > 32 && pl->n_rows > 0) {
+        int vec = 1;
+        if (ldx % 4 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0) vec = 4;
+        else if (ldx % 2 == 0 && (reinterpret_cast<uintptr_t>(x) & 7) == 0) vec = 2;
+        const int S = default_slab(pl->n_cols, a->f, vec);
+        const int tail = a->f % S, main = a->f - tail;
+        if (main > 0 && tail > 0 && tail <= S / 2) {
+            int St = 32;
+            while (St < tail) St *= 2;
+            if (St < S) {
+                sgc_hop_args_t a1 = *a, a2 = *a;
+                a1.f = main; a1.slab_floats = S;
+                a2.f = tail; a2.slab_floats = St;
+                if (a->mean_d) a2.mean_d = a->mean_d + main;
+                if (a->std_d) a2.std_d = a->std_d + main;
+                if (a->partial_d) a2.partial_d = a->partial_d + main;
+                for (int i = 0; i < SGC_MAX_PEERS; ++i)
+                    if (a->peer_y_d[i]) a2.peer_y_d[i] = a->peer_y_d[i] + main;
+                int32_t rc = run_hop(pl, &a1, x, ldx, y, ldy, flags, push_peers, s);
+                if (rc != SGC_OK) return rc;
+                return run_hop(pl, &a2, x + main, ldx, y + main, ldy, flags, push_peers, s);
+            }
+        }
+    }
+    return run_hop(pl, a, x, ldx, y, ldy, flags, push_peers, s);
+}
+
 }  // namespace sgc
 
 using namespace sgc;
@@ -415,8 +451,8 @@ int64_t sgc_spmm_plan_partial_rows(const sgc_plan_t *plan) { return plan ? plan-
 int32_t sgc_spmm_hop(const sgc_plan_t *plan, const sgc_hop_args_t *args, void *stream)
 {
     SGC_REQUIRE(plan && args, "spmm_hop: null plan or args");
-    return run_hop(&plan->impl, args, args->x_d, args->ldx, args->y_d, args->ldy, args->flags, true,
-                   as_stream(stream));
+    return run_hop_auto(&plan->impl, args, args->x_d, args->ldx, args->y_d, args->ldy, args->flags, true,
+                        as_stream(stream));
 }
 
 int32_t sgc_precompute(const sgc_plan_t *plan, const sgc_hop_args_t *args, int32_t k_hops,
@@ -436,7 +472,7 @@ int32_t sgc_precompute(const sgc_plan_t *plan, const sgc_hop_args_t *args, int32
         float *dst = last ? args->y_d : ((k & 1) ? buf_b_d : buf_a_d);
         const int64_t ld_dst = last ? args->ldy : ld_buf;
         const uint32_t flags = (k == 0) ? args->flags : (args->flags & ~std_bits);
-        int32_t rc = run_hop(&plan->impl, args, src, ld_src, dst, ld_dst, flags, false, s);
+        int32_t rc = run_hop_auto(&plan->impl, args, src, ld_src, dst, ld_dst, flags, false, s);
         if (rc != SGC_OK) return rc;
         src = dst;
         ld_src = ld_dst;

@@ -375,6 +375,149 @@ def local_rows_of(graph_csr, row0, row1):
     return (row_ptr[row0:row1 + 1] - b).contiguous(), col[b:e].contiguous(), val[b:e].contiguous()
 
 
+# --------------------------------------------------------------------------------------------------
+# Feature-sharded propagation: S replicated, X split by COLUMNS.  Column c of S^K X depends on column
+# c of X only, so the K hops of a column block need no exchange at all -- not even the Reddit
+# standardisation (utils.py:119 is per column).  This is the sharding of choice whenever S fits on
+# every GPU and the per-GPU block stays wide enough for efficient gathers; row sharding (above) is
+# for adjacencies that exceed one GPU or for narrow feature matrices.
+FEATURE_UNIT = 16            # floats: blocks are multiples of 64 bytes so that gathers stay sector-aligned
+
+
+def partition_features(f, world, unit=FEATURE_UNIT):
+    """Contiguous column blocks [(c0, c1)] in units of `unit` floats, sizes differing by at most one
+    unit; trailing ranks may be empty when f is small."""
+    units = (int(f) + unit - 1) // unit
+    base, extra = divmod(units, world)
+    out, c = [], 0
+    for r in range(world):
+        w = (base + (1 if r < extra else 0)) * unit
+        out.append((min(c, f), min(c + w, f)))
+        c += w
+    return out
+
+
+def choose_sharding(n, nnz, f, world, mem_bytes=170e9):
+    """'features' when a replica of S (12 B per entry + row pointers) plus two N x F/world buffers fit on
+    each GPU and every GPU gets at least 64 columns (256-byte gathers); else 'rows'."""
+    forced = os.environ.get("SGC_B200_SHARDING")
+    if forced in ("rows", "features"):
+        return forced
+    widest = max(c1 - c0 for c0, c1 in partition_features(f, world))
+    fits = nnz * 20.0 + n * 8.0 + 3.0 * n * _pad8(widest) * 4.0 < mem_bytes
+    return "features" if (fits and f // world >= 64) else "rows"
+
+
+def propagate_feature_sharded(graph, x_cols, degree, **kw):
+    """K hops on this rank's column block [N, fc] of X with the full S: no communication.  Returns
+    the same columns of S^K X, bit-identical to those columns of the single-GPU result."""
+    from .propagate import propagate
+    return propagate(graph, x_cols, degree, **kw)
+
+
+def run_feature_sharded_workload(name, args, rank, world, dev, B, with_e2e=True, want_single=True):
+    """bench leg for sharding == 'features' (see run_sharded_workload for the contract)."""
+    from . import _ffi, synth
+    from .features import StandardizedFeatures, col_stats, standardize_, to_padded
+    from .graph import normalize_csr
+    from .propagate import default_chunk, propagate, sgc_precompute
+    shape = synth.SHAPES[name]
+    n, f, k = shape["n"], shape["f"], shape["k"]
+    c0, c1 = partition_features(f, world)[rank]
+    s = synth.make_shape(name, device=dev, with_features=False, lam=bench_lambda())
+    x = synth.gaussian_features(n, f, seed=1, scaled=shape["scaled"], device=dev)
+    x_raw_local = x[:, c0:c1].contiguous()
+    if shape["scaled"]:
+        mean, std = col_stats(x)
+        standardize_(x, mean, std)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    graph = normalize_csr(n, s["row_ptr"], s["col"], s["val"])
+    torch.cuda.synchronize()
+    normalise_ms = (time.perf_counter() - t0) * 1e3
+    single = None
+    if rank == 0 and want_single:
+        xp = to_padded(x)
+        for _ in range(3):
+            propagate(graph, xp, k)
+        torch.cuda.synchronize()
+        ms1 = _device_ms(lambda: propagate(graph, xp, k), 5)
+        single = {"n_gpus": 1, "ms_per_step": ms1, "value": k * graph.nnz * f / (ms1 * 1e-3)}
+        del xp
+    x_local = to_padded(x[:, c0:c1]) if c1 > c0 else None
+    del x
+    torch.cuda.empty_cache()
+    nnz = graph.nnz
+    graph.plan(default_chunk())
+
+    def step():
+        return propagate(graph, x_local, k) if x_local is not None else None
+
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize()
+    dist.barrier()
+    sampler = B["ClockSampler"](dev.index)
+    sampler.start()
+    launches0 = _ffi.launch_count()
+    torch.cuda.synchronize()
+    dist.barrier()
+    start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    start.record()
+    for _ in range(args.steps):
+        step()
+    stop.record()
+    torch.cuda.synchronize()
+    dist.barrier()
+    ms = torch.tensor([start.elapsed_time(stop)], dtype=torch.float64, device=dev)
+    dist.all_reduce(ms, op=dist.ReduceOp.MAX)            # max over ranks, device-timed
+    launches = _ffi.launch_count() - launches0
+    clocks = sampler.stop()
+    ms_per_step = float(ms.item()) / args.steps
+    out = {"name": name, "n": n, "f": f, "k": k, "nnz": nnz, "n_pad": n, "mode": "features",
+           "push_fraction": 0.0, "n_blocks": 1, "normalise_ms": normalise_ms, "ms_per_step": ms_per_step,
+           "value": k * nnz * f / (ms_per_step * 1e-3), "launches": int(launches), "clocks": clocks,
+           "single": single, "e2e": None, "cols_per_rank": max(b - a for a, b in partition_features(f, world))}
+    if with_e2e and x_local is not None:
+        host = {kk: s[kk].cpu().pin_memory() for kk in ("row_ptr", "col", "val")}
+        host["x"] = x_raw_local.cpu().pin_memory()
+        out_host = torch.empty((n, c1 - c0), dtype=torch.float32).pin_memory()
+
+        def e2e_step():
+            g2 = normalize_csr(n, host["row_ptr"].to(dev, non_blocking=True), host["col"].to(dev, non_blocking=True),
+                               host["val"].to(dev, non_blocking=True))
+            xl = to_padded(host["x"], dev)
+            feats = xl
+            if shape["scaled"]:
+                m2, s2 = col_stats(xl)                     # per column: local to this rank's block
+                feats = StandardizedFeatures(xl, m2, s2)
+            y, _ = sgc_precompute(feats, g2, k)
+            out_host.copy_(y, non_blocking=True)
+            torch.cuda.synchronize()
+
+        e2e_step()
+        dist.barrier()
+        e2e_steps = max(2, min(args.steps, 3))
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            e2e_step()
+        dist.barrier()
+        e2e_s = torch.tensor([(time.perf_counter() - t0) / e2e_steps], dtype=torch.float64, device=dev)
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+        h2d = torch.tensor([sum(t.numel() * t.element_size() for t in host.values())], dtype=torch.int64, device=dev)
+        dist.all_reduce(h2d)
+        out["e2e"] = {"value": k * nnz * f / float(e2e_s.item()), "unit": B["UNIT"],
+                      "h2d_bytes_per_step": int(h2d.item()), "d2h_bytes_per_step": int(n * f * 4),
+                      "ms_per_step": float(e2e_s.item()) * 1e3}
+    elif with_e2e:
+        dist.barrier(); dist.barrier()
+        z = torch.zeros(1, dtype=torch.float64, device=dev); dist.all_reduce(z, op=dist.ReduceOp.MAX)
+        z = torch.zeros(1, dtype=torch.int64, device=dev); dist.all_reduce(z)
+    del graph, x_local, s
+    torch.cuda.empty_cache()
+    return out
+
+
 def _device_ms(fn, reps):
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     a.record()
@@ -446,10 +589,15 @@ def _workload_inputs(name, rank, world, dev, want_single):
 
 
 def run_sharded_workload(name, args, rank, world, dev, B, with_e2e=True, want_single=True):
-    """Times K-hop row-sharded propagation of one named workload on `world` GPUs (strong scaling:
-    the graph is fixed, rows are split over the ranks).  Returns the measurements on rank 0."""
-    from . import _ffi
+    """Times K-hop sharded propagation of one named workload on `world` GPUs (strong scaling: the
+    graph is fixed; rows or feature columns are split over the ranks, see choose_sharding).
+    Returns the measurements on rank 0."""
+    from . import _ffi, synth
     from .propagate import default_chunk
+    shape = synth.SHAPES[name]
+    approx_nnz = shape["pairs"] * (2 if shape["symmetric"] else 1) + shape["n"]
+    if choose_sharding(shape["n"], approx_nnz, shape["f"], world) == "features":
+        return run_feature_sharded_workload(name, args, rank, world, dev, B, with_e2e, want_single)
     n, f, k, n_pad, rp, col, val, x_local, single = _workload_inputs(name, rank, world, dev, want_single)
     torch.cuda.synchronize()
     t0 = time.perf_counter()
@@ -534,6 +682,10 @@ def run_sharded_workload(name, args, rank, world, dev, B, with_e2e=True, want_si
 
 
 def _parallelism_text(r, world):
+    if r["mode"] == "features":
+        return ("feature-sharded x%d: S replicated on every GPU, X split into contiguous column blocks of <= %d "
+                "columns; column c of S^K X depends on column c of X only, so the K hops (and the per-column "
+                "standardisation) need no exchange; output column-sharded" % (world, r.get("cols_per_rank", 0)))
     if r["mode"] == "push":
         return ("row-sharded x%d; exchange fused into the SpMM kernel: every output row is staged in shared memory "
                 "and written by cp.async.bulk to all peers' next-hop operands over NVLink (CUDA-IPC mapped), one "

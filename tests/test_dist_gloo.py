@@ -94,3 +94,19 @@ def test_partition_rows():
         for rank, (r0, r1) in enumerate(parts):
             if r1 > r0:
                 assert r0 == rank * n_pad
+
+
+def test_partition_features_and_sharding_choice():
+    from sgc_b200.dist import FEATURE_UNIT, choose_sharding, partition_features
+    for f, world in ((602, 8), (602, 2), (100, 8), (128, 8), (1433, 4), (7, 3), (16, 1)):
+        parts = partition_features(f, world)
+        assert len(parts) == world and parts[0][0] == 0 and parts[-1][1] == f
+        assert all(a[1] == b[0] for a, b in zip(parts, parts[1:]))
+        widths = [b - a for a, b in parts]
+        assert all(a % FEATURE_UNIT == 0 for a, _ in parts if a < f)       # blocks start sector-aligned
+        assert max(widths) - min(w for w in widths if w or True) <= 2 * FEATURE_UNIT
+    # Reddit shape: S fits everywhere and blocks stay wide -> columns; narrow products/papers -> rows
+    assert choose_sharding(232965, 23.4e6, 602, 8) == "features"
+    assert choose_sharding(2449029, 126e6, 100, 8) == "rows"
+    assert choose_sharding(111059956, 1.75e9, 128, 8) == "rows"
+    assert choose_sharding(232965, 23.4e6, 602, 8, mem_bytes=1e8) == "rows"   # S replica does not fit
