@@ -126,8 +126,9 @@ def needed_by_peers(sg, group=None):
     return mask
 
 
-def _pad8(f):
-    return (f + 7) // 8 * 8
+def _pad8(f):          # historical name: the padded leading dimension, see features.pad_ld
+    from .features import pad_ld
+    return pad_ld(f)
 
 
 class _DeviceMemory(object):

@@ -55,8 +55,9 @@ def fused_norm():
     return _ENV("SGC_B200_FUSED_NORM", "0") == "1"
 
 
-def _pad8(f):
-    return (f + 7) // 8 * 8
+def _pad8(f):          # historical name: the padded leading dimension, see features.pad_ld
+    from .features import pad_ld
+    return pad_ld(f)
 
 
 def as_graph(adj):
