@@ -11,7 +11,8 @@
  *   utils.py:23-30          sparse_mx_to_torch_sparse_tensor -> sgc_norm_build (fp32 view), sgc_csr_to_coo
  *   utils.py:92-97          sgc_precompute (K x torch.spmm) -> sgc_spmm_plan_* / sgc_spmm_hop / sgc_precompute
  *   utils.py:118-119        Reddit feature standardisation   -> sgc_col_stats (+ fused into sgc_spmm_hop)
- *   (graph preparation and multi-GPU entry points are added below as they are built)
+ *   utils.py:63,116-117     symmetrisation, induced sub-graph        -> sgc_sort_* / sgc_coo_reduce_* / sgc_subgraph_*
+ *   (no counterpart)        row-sharded multi-GPU propagation        -> sgc_symm_* / sgc_ipc_* / sgc_push_*
  *
  * Conventions
  *   - plain C types only; every pointer named *_d / documented "device" is a CUDA device
@@ -216,6 +217,42 @@ int32_t sgc_spmm_hop(const sgc_plan_t *plan, const sgc_hop_args_t *args, void *s
  * args->y_d.  The standardisation flags apply to the first hop only.  Square matrices only. */
 int32_t sgc_precompute(const sgc_plan_t *plan, const sgc_hop_args_t *args, int32_t k_hops,
                        float *buf_a_d, float *buf_b_d, int64_t ld_buf, void *stream);
+
+/* ---- graph preparation: the loader steps right before the normalisation ------
+ *   adj + adj.T                         utils.py:116      sort the doubled COO stream, sum pairs
+ *   max(adj, adj.T)                     utils.py:63       same, op = max
+ *   adj[idx, :][:, idx]                 utils.py:117      sgc_subgraph_*
+ *   unsorted / duplicated CSR input     (scipy sum_duplicates)   sort + reduce
+ * Building block: stable LSD radix sort of (key, int32, fp64) triples by an int32 key in
+ * [0, 2^key_bits), 8 bits per pass; payload arrays may be NULL (in/out together).  Sorting a COO
+ * stream by column, then by row, leaves it row-major with ascending columns and equal pairs
+ * adjacent in their original order. */
+size_t  sgc_sort_workspace_bytes(int64_t n);
+int32_t sgc_sort_by_key_i32(int64_t n, int32_t key_bits, const int32_t *key_in_d, const int32_t *p32_in_d,
+                            const double *p64_in_d, int32_t *key_out_d, int32_t *p32_out_d,
+                            double *p64_out_d, void *ws_d, size_t ws_bytes, void *stream);
+/* rows_out_d[p] = row_offset + (row that stores entry p): COO row indices of a CSR, int32. */
+int32_t sgc_csr_expand_rows(int64_t n, const int64_t *row_ptr_d, int32_t row_offset, int32_t *rows_out_d,
+                            void *stream);
+/* Row-major sorted COO stream (duplicates adjacent) -> canonical CSR.  op 0: a run of equal pairs
+ * is summed in stored order (scipy sum_duplicates / csr_plus_csr); op 1: maximum of the run.
+ * drop_zeros: results that compare equal to 0 are dropped (scipy's binary operators do).
+ * Outputs sized for n entries; the new nnz is row_ptr_out_d[n_rows]. */
+size_t  sgc_coo_reduce_workspace_bytes(int64_t n);
+int32_t sgc_coo_reduce_to_csr(int64_t n, int64_t n_rows, const int32_t *row_d, const int32_t *col_d,
+                              const double *val_d, int32_t op, int32_t drop_zeros, int64_t *row_ptr_out_d,
+                              int32_t *col_out_d, double *val_out_d, void *ws_d, size_t ws_bytes, void *stream);
+/* Induced sub-matrix M[idx, :][:, idx] for a list idx of m distinct row/column ids (int64, any
+ * order): colmap_d[n_cols] <- position of each id in idx or -1; count -> scanned row_ptr_out_d[m+1];
+ * fill -> (col, val) with new column ids, in the stored order of each selected row (ascending when
+ * idx is ascending; otherwise sort + reduce afterwards). */
+int32_t sgc_subgraph_colmap(int64_t n_cols, int64_t m, const int64_t *idx_d, int32_t *colmap_d, void *stream);
+int32_t sgc_subgraph_count(int64_t m, const int64_t *idx_d, const int64_t *row_ptr_d, const int32_t *col_d,
+                           const int32_t *colmap_d, int64_t *row_ptr_out_d, void *ws_d, size_t ws_bytes,
+                           void *stream);
+int32_t sgc_subgraph_fill(int64_t m, const int64_t *idx_d, const int64_t *row_ptr_d, const int32_t *col_d,
+                          const double *val_d, const int32_t *colmap_d, const int64_t *row_ptr_out_d,
+                          int32_t *col_out_d, double *val_out_d, void *stream);
 
 /* ---- K5: row-sharded multi-GPU propagation (north_star (3); no counterpart in the reference) ---
  * One process per GPU.  Every rank owns a contiguous row range of S and keeps two full-height

@@ -232,14 +232,21 @@ def augment_csr(n_rows, n_cols, row_offset, row_ptr, col, val):
         if int(flag.item()) == 0:
             if nnz and (int(col.min().item()) < 0 or int(col.max().item()) >= n_cols):
                 raise ValueError("column index out of range")
-            ws = _ws(lib.sgc_csr_canonicalize_workspace_bytes(n, nnz), dev)
-            rp2 = torch.empty(n + 1, dtype=torch.int64, device=dev)
-            col2 = torch.empty(nnz, dtype=torch.int32, device=dev)
-            val2 = torch.empty(nnz, dtype=torch.float64, device=dev)
-            _ffi.call("sgc_csr_canonicalize", n, nnz, _ffi.ptr(row_ptr), _ffi.ptr(col), _ffi.ptr(val),
-                      _ffi.ptr(rp2), _ffi.ptr(col2), _ffi.ptr(val2), _ffi.ptr(ws), ws.numel(), s)
-            nnz = int(rp2[n].item())
-            row_ptr, col, val = rp2, col2[:nnz], val2[:nnz]
+            if nnz > (1 << 18):
+                # large input: radix sort of the COO stream (prep.py); the per-row rank sort below
+                # is quadratic in the row length
+                from .prep import canonicalize
+                row_ptr, col, val = canonicalize(n, n_cols, row_ptr, col, val)
+                nnz = int(col.numel())
+            else:
+                ws = _ws(lib.sgc_csr_canonicalize_workspace_bytes(n, nnz), dev)
+                rp2 = torch.empty(n + 1, dtype=torch.int64, device=dev)
+                col2 = torch.empty(nnz, dtype=torch.int32, device=dev)
+                val2 = torch.empty(nnz, dtype=torch.float64, device=dev)
+                _ffi.call("sgc_csr_canonicalize", n, nnz, _ffi.ptr(row_ptr), _ffi.ptr(col), _ffi.ptr(val),
+                          _ffi.ptr(rp2), _ffi.ptr(col2), _ffi.ptr(val2), _ffi.ptr(ws), ws.numel(), s)
+                nnz = int(rp2[n].item())
+                row_ptr, col, val = rp2, col2[:nnz], val2[:nnz]
         # K1: A + I
         rp_aug = torch.empty(n + 1, dtype=torch.int64, device=dev)
         _ffi.call("sgc_csr_selfloop_count", n, row_offset, _ffi.ptr(row_ptr), _ffi.ptr(col), _ffi.ptr(val),

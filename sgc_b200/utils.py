@@ -23,8 +23,9 @@ import torch
 
 from . import _ffi
 from .features import StandardizedFeatures, col_stats, to_padded
-from .graph import SgcGraph, require_cuda
-from .normalization import fetch_normalization, row_normalize
+from .graph import SgcGraph, normalize_csr, require_cuda, upload_csr
+from .normalization import aug_normalized_adjacency, fetch_normalization, row_normalize
+from .prep import induced_subgraph, symmetrize
 from .propagate import sgc_precompute  # noqa: F401  (re-exported: the reference's utils.sgc_precompute)
 
 
@@ -139,13 +140,18 @@ def load_reddit_data(data_path="data/", normalization="AugNormAdj", cuda=True):
     labels[train_index] = y_train
     labels[val_index] = y_val
     labels[test_index] = y_test
-    adj = adj + adj.T                                           # utils.py:116
-    train_adj = adj[train_index, :][:, train_index]             # utils.py:117
     raw = to_padded(torch.from_numpy(np.ascontiguousarray(feats, dtype=np.float32)), dev)
     mean, std = col_stats(raw)                                  # utils.py:119 statistics (K3)
-    features = StandardizedFeatures(raw, mean, std)             # standardisation fused into hop 1
+    features = StandardizedFeatures(raw, mean, std)             # standardised in place before hop 1
     normalizer = fetch_normalization(normalization)
-    adj = normalizer(adj)                                       # K1 + K2 on the GPU
-    train_adj = normalizer(train_adj)
+    if normalizer is not aug_normalized_adjacency:              # unknown name: fail as the reference does
+        adj = normalizer(adj + adj.T)
+    # graph preparation on the GPU (prep.py): the raw adjacency goes up once
+    shape, rp, col, val = upload_csr(adj, dev)
+    n = shape[0]
+    rp, col, val = symmetrize(n, rp, col, val, op="sum")                        # utils.py:116  adj + adj.T
+    trp, tcol, tval = induced_subgraph(n, n, rp, col, val, train_index)         # utils.py:117
+    adj = normalize_csr(n, rp, col, val)                                        # K1 + K2
+    train_adj = normalize_csr(len(train_index), trp, tcol, tval)
     labels = torch.from_numpy(labels).long().to(dev)
     return adj, train_adj, features, labels, train_index, val_index, test_index
