@@ -346,8 +346,8 @@ def run_own(args):
                                   chunk=sgc_b200.propagate.default_chunk(),
                                   weights=("fp32((d_i*a_ij)*d_j) formed in the hop kernel (SGC_B200_FUSED_NORM=1)"
                                            if sgc_b200.propagate.fused_norm() else
-                                           "fp32 S values written once by sgc_norm_build (%.3f ms, outside the timed "
-                                           "hops like the reference's normalisation), streamed by every hop" % sval_ms),
+                                           "fp32 S values written once by sgc_norm_values (inside normalise_ms, outside "
+                                           "the timed hops like the reference's normalisation), streamed by every hop"),
                                   timed_region="K hops on device-resident CSR + standardised X, as "
                                                "utils.py:93-96 times them; K1/K2/K3 + standardisation "
                                                "timed separately (above) and inside e2e"),
@@ -391,7 +391,6 @@ def run_e2e(args, s, name, k, nnz_s, dev):
     (K1+K2), computes the column statistics (K3), runs the K hops and reads the propagated
     features back to pinned host memory."""
     import sgc_b200
-    from sgc_b200.features import StandardizedFeatures
     n, f = s["n"], s["f"]
     host = {kk: s[kk].cpu().pin_memory() for kk in ("row_ptr", "col", "val", "x")}
     out_host = torch.empty((n, f), dtype=torch.float32).pin_memory()
@@ -399,18 +398,10 @@ def run_e2e(args, s, name, k, nnz_s, dev):
     d2h = out_host.numel() * 4
 
     def step():
-        rp = host["row_ptr"].to(dev, non_blocking=True)
-        col = host["col"].to(dev, non_blocking=True)
-        val = host["val"].to(dev, non_blocking=True)
-        x = sgc_b200.to_padded(host["x"], dev)          # H2D straight into padded device rows
-        graph = sgc_b200.normalize_csr(n, rp, col, val)
-        feats = x
-        if name == "reddit":
-            mean, std = sgc_b200.col_stats(x)
-            feats = StandardizedFeatures(x, mean, std)
-        y, _ = sgc_b200.sgc_precompute(feats, graph, k)
-        out_host.copy_(y, non_blocking=True)
-        torch.cuda.synchronize()
+        # sgc_b200.precompute_host: CSR(A) up first, K1/K2 overlap the upload of X, the last hop runs
+        # by row blocks whose D2H overlaps the next block (sgc_b200/pipeline.py)
+        sgc_b200.precompute_host((n, host["row_ptr"], host["col"], host["val"]), host["x"], k,
+                                 standardize=(name == "reddit"), out=out_host)
 
     steps = max(2, min(args.steps, 5))
     step()
@@ -420,7 +411,10 @@ def run_e2e(args, s, name, k, nnz_s, dev):
     secs = (time.perf_counter() - t0) / steps
     return {"value": k * nnz_s * f / secs, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
             "d2h_bytes_per_step": int(d2h), "ms_per_step": secs * 1e3, "steps": steps,
-            "path": "host CSR(A)+X -> H2D -> aug_normalized_adjacency (K1,K2) -> col_stats (K3) -> sgc_precompute -> D2H"}
+            "path": "sgc_b200.precompute_host: pinned host CSR(A)+X -> H2D -> aug_normalized_adjacency (K1,K2, "
+                    "overlapped with the upload of X) -> col_stats + standardise (K3) -> K hops (last hop in %d "
+                    "row blocks, each copied back while the next is computed) -> pinned host result"
+                    % sgc_b200.pipeline.default_out_blocks()}
 
 
 def main():

@@ -55,6 +55,15 @@ int64_t sgc_launch_count(void);
  * device maximum; the granted size is written to granted_out (may be NULL).  Process-wide. */
 int32_t sgc_l2_set_persisting_bytes(int64_t bytes, int64_t *granted_out);
 
+/* ---- column-slab transfers (utils.py:82-88,126-130: the reference's .cuda() / .cpu() copies) -------
+ * Strided 2-D copy on the DMA engines (cudaMemcpy2DAsync, direction inferred from the pointers):
+ * `rows` pieces of `width_bytes` each, `src_pitch_bytes` / `dst_pitch_bytes` apart.  Moves one
+ * feature-column slab of a row-major [N, F] matrix between pinned host memory and padded device
+ * rows, so that the hops of slab c (columns are independent under S X) run while slab c+1 is
+ * still crossing PCIe.  Host memory must be pinned for the copy to be asynchronous. */
+int32_t sgc_copy_2d(void *dst, int64_t dst_pitch_bytes, const void *src, int64_t src_pitch_bytes,
+                    int64_t width_bytes, int64_t rows, void *stream);
+
 /* ---- generic device primitives ------------------------------------------------------------ */
 size_t  sgc_scan_workspace_bytes(int64_t n);
 /* In-place exclusive prefix sum of data_d[0..n) (int64). */
@@ -87,6 +96,24 @@ int32_t sgc_csr_selfloop_build(int64_t n, int64_t diag_offset, const int64_t *ro
                                const int64_t *row_ptr_out_d, int32_t *col_out_d,
                                double *aval_out_d, void *stream);
 
+/* Fast path of K1 for canonical input (what every loader of the reference produces): element-
+ * parallel, so hub rows cost no more than short ones.
+ * count: one pass over (col, val) that (a) proves the input canonical -- row_ptr monotone from 0 to
+ * nnz, strictly ascending columns in [0, n_cols) -- (b) detects entries A + I would drop (exact
+ * zeros, a_ii == -1) and (c) records in info_d[n] where each row's self-loop goes; then
+ * row_ptr_out_d[n+1] = scan(len_i + (row i lacks its diagonal)).  summary_d[0] (device int64) gets
+ * flag bits: 1 = not canonical, 2 = has dropped entries -- if either is set the outputs are
+ * unusable and the caller takes the general path above (sgc_csr_canonicalize / _selfloop_*);
+ * summary_d[1] = nnz of A + I.  build: element-wise map (col, val) -> (col_out, aval_out). */
+int32_t sgc_csr_augment_count(int64_t n, int64_t n_cols, int64_t diag_offset, int64_t nnz,
+                              const int64_t *row_ptr_d, const int32_t *col_d, const double *val_d,
+                              int32_t *info_d, int64_t *row_ptr_out_d, int64_t *summary_d, void *ws_d,
+                              size_t ws_bytes, void *stream);
+int32_t sgc_csr_augment_build(int64_t n, int64_t diag_offset, int64_t nnz, const int64_t *row_ptr_d,
+                              const int32_t *col_d, const double *val_d, const int32_t *info_d,
+                              const int64_t *row_ptr_out_d, int32_t *col_out_d, double *aval_out_d,
+                              void *stream);
+
 /* ---- K2: degree reduction and D^-1/2            (normalization.py:8-10) ------------------- */
 /* rowsum_d[i] = sum of row i of A+I accumulated in stored order in fp64; dinv_d[i] =
  * rowsum^-1/2 (correctly rounded), +inf -> 0 (normalization.py:10); NaN for negative sums.
@@ -112,6 +139,13 @@ int32_t sgc_norm_build(int64_t n, const int64_t *row_ptr_d, const int32_t *col_d
                        const double *aval_d, const double *dinv_rows_d, const double *dinv_d,
                        const int64_t *row_ptr_out_d, int32_t *col_out_d, double *aval_out_d,
                        double *s64_out_d, float *s32_out_d, void *stream);
+/* Fast path: values only, element-parallel.  s64_out_d / s32_out_d (either may be NULL) as in
+ * sgc_norm_build; zero_flag_d[0] (device int64) <- 1 if any product is exactly zero, i.e. scipy
+ * would prune the structure: the caller then runs sgc_norm_count + sgc_norm_build.  row_ptr_d[0]
+ * must be 0 and row_ptr_d[n] == nnz. */
+int32_t sgc_norm_values(int64_t n, int64_t nnz, const int64_t *row_ptr_d, const int32_t *col_d,
+                        const double *aval_d, const double *dinv_rows_d, const double *dinv_d,
+                        double *s64_out_d, float *s32_out_d, int64_t *zero_flag_d, void *stream);
 /* CSR row pointers -> COO row indices (int64), and int32 -> int64 columns: the [2, nnz] index
  * tensor of utils.py:26-27.  idx_out_d has 2*nnz int64 (rows then cols). */
 int32_t sgc_csr_to_coo(int64_t n, const int64_t *row_ptr_d, const int32_t *col_d, int64_t nnz,

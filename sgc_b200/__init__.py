@@ -7,6 +7,8 @@ from .graph import (SgcGraph, augment_csr, finish_normalization, from_scipy, fro
 from .features import StandardizedFeatures, col_stats, standardize_, to_padded  # noqa: F401
 from . import propagate  # noqa: F401  (module: propagate.propagate() is the stream-ordered K-hop call)
 from .propagate import hop, sgc_precompute  # noqa: F401
+from . import pipeline  # noqa: F401
+from .pipeline import precompute_host  # noqa: F401
 from .normalization import aug_normalized_adjacency, fetch_normalization, row_normalize  # noqa: F401
 
 __version__ = "0.1.0"

@@ -41,6 +41,7 @@ SIGNATURES = {
     "sgc_device_check": (c_i32, [c_i32]),
     "sgc_launch_count": (c_i64, []),
     "sgc_l2_set_persisting_bytes": (c_i32, [c_i64, ctypes.POINTER(c_i64)]),
+    "sgc_copy_2d": (c_i32, [c_p, c_i64, c_p, c_i64, c_i64, c_i64, c_p]),
     "sgc_scan_workspace_bytes": (c_sz, [c_i64]),
     "sgc_scan_exclusive_i64": (c_i32, [c_p, c_i64, c_p, c_sz, c_p]),
     "sgc_csr_check_canonical": (c_i32, [c_i64, c_i64, c_p, c_p, c_p, c_p]),
@@ -48,6 +49,9 @@ SIGNATURES = {
     "sgc_csr_canonicalize": (c_i32, [c_i64, c_i64, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_sz, c_p]),
     "sgc_csr_selfloop_count": (c_i32, [c_i64, c_i64, c_p, c_p, c_p, c_p, c_p, c_sz, c_p]),
     "sgc_csr_selfloop_build": (c_i32, [c_i64, c_i64, c_p, c_p, c_p, c_p, c_p, c_p, c_p]),
+    "sgc_csr_augment_count": (c_i32, [c_i64, c_i64, c_i64, c_i64, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_sz, c_p]),
+    "sgc_csr_augment_build": (c_i32, [c_i64, c_i64, c_i64, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p]),
+    "sgc_norm_values": (c_i32, [c_i64, c_i64, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p]),
     "sgc_degree_inv_sqrt": (c_i32, [c_i64, c_p, c_p, c_p, c_p, c_p]),
     "sgc_norm_count": (c_i32, [c_i64, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_sz, c_p]),
     "sgc_norm_build": (c_i32, [c_i64, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p]),

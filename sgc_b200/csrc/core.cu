@@ -184,4 +184,17 @@ int32_t sgc_scan_exclusive_i64(int64_t *data_d, int64_t n, void *ws_d, size_t ws
     return sgc::scan_exclusive_i64(data_d, n, ws_d, ws_bytes, sgc::as_stream(stream));
 }
 
+int32_t sgc_copy_2d(void *dst, int64_t dst_pitch_bytes, const void *src, int64_t src_pitch_bytes,
+                    int64_t width_bytes, int64_t rows, void *stream)
+{
+    if (rows == 0 || width_bytes == 0) return SGC_OK;
+    SGC_REQUIRE(dst && src && rows > 0 && width_bytes > 0 && dst_pitch_bytes >= width_bytes &&
+                    src_pitch_bytes >= width_bytes,
+                "copy_2d: bad arguments");
+    SGC_CUDA_TRY(cudaMemcpy2DAsync(dst, (size_t)dst_pitch_bytes, src, (size_t)src_pitch_bytes,
+                                   (size_t)width_bytes, (size_t)rows, cudaMemcpyDefault,
+                                   sgc::as_stream(stream)));
+    return SGC_OK;
+}
+
 }  // extern "C"

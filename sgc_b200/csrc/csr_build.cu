@@ -7,8 +7,12 @@
 //
 //   selfloop_count / selfloop_build : row_ptr / col_idx of A+I, bit-exact against scipy's CSR
 //                                     (existing diagonal merged, exact-zero results dropped)
-//   degree_inv_sqrt                 : r_i = sum_j (A+I)_ij in stored order (fp64), d_i = r_i^-1/2
+//   (degrees: csr_fast.cu)
 //   norm_count / norm_build         : structure after scipy's zero-product pruning + S values
+//
+// These are the GENERAL kernels: they handle entries that A + I drops and zero-product pruning.  For
+// canonical input without such entries (every benchmark graph, every citation graph) the host takes
+// the element-parallel fast path of csr_fast.cu and never launches them.
 //
 // Rows are handled by groups of 8 lanes (4 rows per warp): citation graphs have ~5 entries per
 // row, Reddit ~100, hubs ~20k; 8 lanes keep loads coalesced in 32-/64-byte pieces without idling
@@ -122,32 +126,6 @@ selfloop_build_kernel(int64_t n, int64_t doff, const int64_t *__restrict__ row_p
             col_out[w] = dc;
             val_out[w] = 1.0;
         }
-    }
-}
-
-// One thread per row, sequential fp64 accumulation in stored order: this is the order
-// scipy's coo_matvec uses for adj.sum(1) (normalization.py:8), so real-valued weights give the
-// same bits.  Loads are independent of the add chain and are issued four at a time.
-__global__ void __launch_bounds__(ROW_THREADS)
-degree_inv_sqrt_kernel(int64_t n, const int64_t *__restrict__ row_ptr,
-                       const double *__restrict__ aval, double *__restrict__ rowsum,
-                       double *__restrict__ dinv)
-{
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
-         i += (int64_t)gridDim.x * blockDim.x) {
-        const int64_t b = row_ptr[i], e = row_ptr[i + 1];
-        double r = 0.0;
-        int64_t p = b;
-        for (; p + 4 <= e; p += 4) {
-            const double v0 = aval[p], v1 = aval[p + 1], v2 = aval[p + 2], v3 = aval[p + 3];
-            r = __dadd_rn(r, v0);
-            r = __dadd_rn(r, v1);
-            r = __dadd_rn(r, v2);
-            r = __dadd_rn(r, v3);
-        }
-        for (; p < e; ++p) r = __dadd_rn(r, aval[p]);
-        if (rowsum) rowsum[i] = r;
-        dinv[i] = rsqrt_refined(r);
     }
 }
 
@@ -419,17 +397,6 @@ int32_t sgc_csr_selfloop_build(int64_t n, int64_t diag_offset, const int64_t *ro
     SGC_REQUIRE(col_out_d && aval_out_d, "csr_selfloop_build: null outputs");
     selfloop_build_kernel<<<grid_for(ceil_div(n, ROWS_PER_BLOCK), 8), ROW_THREADS, 0, as_stream(stream)>>>(
         n, diag_offset, row_ptr_d, col_d, val_d, row_ptr_out_d, col_out_d, aval_out_d);
-    SGC_LAUNCH_CHECK();
-    return SGC_OK;
-}
-
-int32_t sgc_degree_inv_sqrt(int64_t n, const int64_t *row_ptr_d, const double *aval_d,
-                            double *rowsum_d, double *dinv_d, void *stream)
-{
-    SGC_REQUIRE(n >= 0 && row_ptr_d && dinv_d, "degree_inv_sqrt: bad arguments");
-    if (n == 0) return SGC_OK;
-    degree_inv_sqrt_kernel<<<grid_for(ceil_div(n, ROW_THREADS), 8), ROW_THREADS, 0, as_stream(stream)>>>(
-        n, row_ptr_d, aval_d, rowsum_d, dinv_d);
     SGC_LAUNCH_CHECK();
     return SGC_OK;
 }

@@ -212,6 +212,47 @@ class _Plan(object):
 
 
 # ---- K1 + K2: normalisation driver ------------------------------------------------------------------
+def _augment_general(n, n_cols, row_offset, row_ptr, col, val, nnz, canonical):
+    """General path of K1 (csr_build.cu): unsorted / duplicated input is canonicalised first, and
+    entries A + I drops (exact zeros, a_ii == -1: scipy's csr_plus_csr prunes them) are compacted
+    away by the row-group kernels.  Returns (row_ptr, col, aval) of A + I."""
+    dev = row_ptr.device
+    lib = _ffi.lib()
+    s = stream_ptr()
+    scan_ws = _ws(lib.sgc_scan_workspace_bytes(n + 1), dev)
+    if not canonical:
+        if nnz and (int(col.min().item()) < 0 or int(col.max().item()) >= n_cols):
+            raise ValueError("column index out of range")
+        rp_host_ok = bool((row_ptr[1:] >= row_ptr[:-1]).all().item()) and int(row_ptr[0].item()) == 0 \
+            and int(row_ptr[n].item()) == nnz if n else True
+        if not rp_host_ok:
+            raise ValueError("row_ptr is not a valid CSR row pointer array")
+        if nnz > (1 << 18):
+            # large input: radix sort of the COO stream (prep.py); the per-row rank sort below
+            # is quadratic in the row length
+            from .prep import canonicalize
+            row_ptr, col, val = canonicalize(n, n_cols, row_ptr, col, val)
+            nnz = int(col.numel())
+        else:
+            ws = _ws(lib.sgc_csr_canonicalize_workspace_bytes(n, nnz), dev)
+            rp2 = torch.empty(n + 1, dtype=torch.int64, device=dev)
+            col2 = torch.empty(nnz, dtype=torch.int32, device=dev)
+            val2 = torch.empty(nnz, dtype=torch.float64, device=dev)
+            _ffi.call("sgc_csr_canonicalize", n, nnz, _ffi.ptr(row_ptr), _ffi.ptr(col), _ffi.ptr(val),
+                      _ffi.ptr(rp2), _ffi.ptr(col2), _ffi.ptr(val2), _ffi.ptr(ws), ws.numel(), s)
+            nnz = int(rp2[n].item())
+            row_ptr, col, val = rp2, col2[:nnz], val2[:nnz]
+    rp_aug = torch.empty(n + 1, dtype=torch.int64, device=dev)
+    _ffi.call("sgc_csr_selfloop_count", n, row_offset, _ffi.ptr(row_ptr), _ffi.ptr(col), _ffi.ptr(val),
+              _ffi.ptr(rp_aug), _ffi.ptr(scan_ws), scan_ws.numel(), s)
+    nnz_aug = int(rp_aug[n].item()) if n else 0
+    col_aug = torch.empty(nnz_aug, dtype=torch.int32, device=dev)
+    aval = torch.empty(nnz_aug, dtype=torch.float64, device=dev)
+    _ffi.call("sgc_csr_selfloop_build", n, row_offset, _ffi.ptr(row_ptr), _ffi.ptr(col), _ffi.ptr(val),
+              _ffi.ptr(rp_aug), _ffi.ptr(col_aug), _ffi.ptr(aval), s)
+    return rp_aug, col_aug, aval
+
+
 def augment_csr(n_rows, n_cols, row_offset, row_ptr, col, val):
     """K1 + K2 on a row slice [row_offset, row_offset + n_rows) of an n_cols x n_cols adjacency with
     global column ids (row_offset = 0 and n_rows == n_cols for a whole matrix): canonical CSR of
@@ -227,35 +268,23 @@ def augment_csr(n_rows, n_cols, row_offset, row_ptr, col, val):
         val = val.to(torch.float64).contiguous()
         nnz = int(col.numel())
         scan_ws = _ws(lib.sgc_scan_workspace_bytes(n + 1), dev)
-        flag = torch.empty(1, dtype=torch.int32, device=dev)
-        _ffi.call("sgc_csr_check_canonical", n, n_cols, _ffi.ptr(row_ptr), _ffi.ptr(col), _ffi.ptr(flag), s)
-        if int(flag.item()) == 0:
-            if nnz and (int(col.min().item()) < 0 or int(col.max().item()) >= n_cols):
-                raise ValueError("column index out of range")
-            if nnz > (1 << 18):
-                # large input: radix sort of the COO stream (prep.py); the per-row rank sort below
-                # is quadratic in the row length
-                from .prep import canonicalize
-                row_ptr, col, val = canonicalize(n, n_cols, row_ptr, col, val)
-                nnz = int(col.numel())
-            else:
-                ws = _ws(lib.sgc_csr_canonicalize_workspace_bytes(n, nnz), dev)
-                rp2 = torch.empty(n + 1, dtype=torch.int64, device=dev)
-                col2 = torch.empty(nnz, dtype=torch.int32, device=dev)
-                val2 = torch.empty(nnz, dtype=torch.float64, device=dev)
-                _ffi.call("sgc_csr_canonicalize", n, nnz, _ffi.ptr(row_ptr), _ffi.ptr(col), _ffi.ptr(val),
-                          _ffi.ptr(rp2), _ffi.ptr(col2), _ffi.ptr(val2), _ffi.ptr(ws), ws.numel(), s)
-                nnz = int(rp2[n].item())
-                row_ptr, col, val = rp2, col2[:nnz], val2[:nnz]
-        # K1: A + I
         rp_aug = torch.empty(n + 1, dtype=torch.int64, device=dev)
-        _ffi.call("sgc_csr_selfloop_count", n, row_offset, _ffi.ptr(row_ptr), _ffi.ptr(col), _ffi.ptr(val),
-                  _ffi.ptr(rp_aug), _ffi.ptr(scan_ws), scan_ws.numel(), s)
-        nnz_aug = int(rp_aug[n].item()) if n else 0
-        col_aug = torch.empty(nnz_aug, dtype=torch.int32, device=dev)
-        aval = torch.empty(nnz_aug, dtype=torch.float64, device=dev)
-        _ffi.call("sgc_csr_selfloop_build", n, row_offset, _ffi.ptr(row_ptr), _ffi.ptr(col), _ffi.ptr(val),
-                  _ffi.ptr(rp_aug), _ffi.ptr(col_aug), _ffi.ptr(aval), s)
+        # fast path (csr_fast.cu): one element-parallel pass proves the input canonical, finds out
+        # whether A + I drops anything, and places every self-loop; one host read-back
+        info = torch.empty(n, dtype=torch.int32, device=dev)
+        summary = torch.empty(2, dtype=torch.int64, device=dev)
+        _ffi.call("sgc_csr_augment_count", n, n_cols, row_offset, nnz, _ffi.ptr(row_ptr), _ffi.ptr(col),
+                  _ffi.ptr(val), _ffi.ptr(info), _ffi.ptr(rp_aug), _ffi.ptr(summary), _ffi.ptr(scan_ws),
+                  scan_ws.numel(), s)
+        flags, nnz_aug = summary.cpu().tolist()
+        if flags == 0:
+            col_aug = torch.empty(nnz_aug, dtype=torch.int32, device=dev)
+            aval = torch.empty(nnz_aug, dtype=torch.float64, device=dev)
+            _ffi.call("sgc_csr_augment_build", n, row_offset, nnz, _ffi.ptr(row_ptr), _ffi.ptr(col),
+                      _ffi.ptr(val), _ffi.ptr(info), _ffi.ptr(rp_aug), _ffi.ptr(col_aug), _ffi.ptr(aval), s)
+        else:
+            rp_aug, col_aug, aval = _augment_general(n, n_cols, row_offset, row_ptr, col, val, nnz,
+                                                     canonical=not (flags & 1))
         # K2: degrees
         rowsum = torch.empty(n, dtype=torch.float64, device=dev)
         dinv = torch.empty(n, dtype=torch.float64, device=dev)
@@ -264,30 +293,42 @@ def augment_csr(n_rows, n_cols, row_offset, row_ptr, col, val):
     return rp_aug, col_aug, aval, rowsum, dinv
 
 
-def finish_normalization(n_rows, n_cols, rp_aug, col_aug, aval, rowsum, dinv_rows, dinv_cols):
+def finish_normalization(n_rows, n_cols, rp_aug, col_aug, aval, rowsum, dinv_rows, dinv_cols, materialize=None):
     """Structure of S after scipy's zero-product pruning (normalization.py:12; it only differs
     from A + I when some D^-1/2 entry is zero) -> `SgcGraph`.  dinv_rows: D^-1/2 of the slice's
     rows; dinv_cols: D^-1/2 of all n_cols columns."""
     dev = require_cuda(rp_aug.device)
     lib = _ffi.lib()
     n = int(n_rows)
+    if materialize is None:
+        import os
+        materialize = os.environ.get("SGC_B200_FUSED_NORM", "0") != "1"
     with torch.cuda.device(dev):
         s = stream_ptr()
-        scan_ws = _ws(lib.sgc_scan_workspace_bytes(n + 1), dev)
-        rp_s = torch.empty(n + 1, dtype=torch.int64, device=dev)
-        dropped = torch.empty(1, dtype=torch.int64, device=dev)
-        _ffi.call("sgc_norm_count", n, _ffi.ptr(rp_aug), _ffi.ptr(col_aug), _ffi.ptr(aval),
-                  _ffi.ptr(dinv_rows), _ffi.ptr(dinv_cols), _ffi.ptr(rp_s), _ffi.ptr(dropped),
-                  _ffi.ptr(scan_ws), scan_ws.numel(), s)
-        if int(dropped.item()) != 0:
-            nnz_s = int(rp_s[n].item())
-            col_s = torch.empty(nnz_s, dtype=torch.int32, device=dev)
-            aval_s = torch.empty(nnz_s, dtype=torch.float64, device=dev)
-            _ffi.call("sgc_norm_build", n, _ffi.ptr(rp_aug), _ffi.ptr(col_aug), _ffi.ptr(aval),
-                      _ffi.ptr(dinv_rows), _ffi.ptr(dinv_cols), _ffi.ptr(rp_s), _ffi.ptr(col_s),
-                      _ffi.ptr(aval_s), None, None, s)
-            rp_aug, col_aug, aval = rp_s, col_s, aval_s
-    return SgcGraph(n, int(n_cols), rp_aug, col_aug, aval, dinv_cols, rowsum=rowsum, dinv_rows=dinv_rows)
+        # fast path: the fp32 values of S in one element-parallel pass, which also reports whether
+        # any product is exactly zero (only then does scipy's CSR product prune the structure)
+        nnz = int(col_aug.numel())
+        sval = torch.empty(nnz, dtype=torch.float32, device=dev) if materialize else None
+        zero = torch.empty(1, dtype=torch.int64, device=dev)
+        _ffi.call("sgc_norm_values", n, nnz, _ffi.ptr(rp_aug), _ffi.ptr(col_aug), _ffi.ptr(aval),
+                  _ffi.ptr(dinv_rows), _ffi.ptr(dinv_cols), None, _ffi.ptr(sval), _ffi.ptr(zero), s)
+        if int(zero.item()) != 0:
+            sval = None
+            scan_ws = _ws(lib.sgc_scan_workspace_bytes(n + 1), dev)
+            rp_s = torch.empty(n + 1, dtype=torch.int64, device=dev)
+            dropped = torch.empty(1, dtype=torch.int64, device=dev)
+            _ffi.call("sgc_norm_count", n, _ffi.ptr(rp_aug), _ffi.ptr(col_aug), _ffi.ptr(aval),
+                      _ffi.ptr(dinv_rows), _ffi.ptr(dinv_cols), _ffi.ptr(rp_s), _ffi.ptr(dropped),
+                      _ffi.ptr(scan_ws), scan_ws.numel(), s)
+            if int(dropped.item()) != 0:
+                nnz_s = int(rp_s[n].item())
+                col_s = torch.empty(nnz_s, dtype=torch.int32, device=dev)
+                aval_s = torch.empty(nnz_s, dtype=torch.float64, device=dev)
+                _ffi.call("sgc_norm_build", n, _ffi.ptr(rp_aug), _ffi.ptr(col_aug), _ffi.ptr(aval),
+                          _ffi.ptr(dinv_rows), _ffi.ptr(dinv_cols), _ffi.ptr(rp_s), _ffi.ptr(col_s),
+                          _ffi.ptr(aval_s), None, None, s)
+                rp_aug, col_aug, aval = rp_s, col_s, aval_s
+    return SgcGraph(n, int(n_cols), rp_aug, col_aug, aval, dinv_cols, rowsum=rowsum, dinv_rows=dinv_rows, sval=sval)
 
 
 def normalize_csr(n, row_ptr, col, val):

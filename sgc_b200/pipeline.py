@@ -1,0 +1,252 @@
+"""Host-to-host precompute: the whole path of the reference's loaders + `sgc_precompute` for data
+that lives in host memory, with the PCIe copies overlapped with the GPU work.
+
+What it replaces, in reference order (paths relative to /root/reference):
+    utils.py:118-119   feature standardisation        (optional, `standardize=True`)
+    utils.py:120-122   aug_normalized_adjacency + sparse_mx_to_torch_sparse_tensor
+    utils.py:126-130   .cuda() of adjacency and features            (H2D)
+    utils.py:92-97     sgc_precompute                               (K hops)
+    reddit.py:71 / citation.py: the propagated features going back to the host consumer (D2H)
+
+Two schedules, both bit-identical to `sgc_precompute` on device-resident inputs
+(tests/test_gpu_parity.py); `in`/`out` are copy streams (one DMA engine per direction), `main`
+carries every kernel.  The adjacency always goes up first, so its normalisation (K1, K2, fp32 S
+values, split plans) runs while the features are still crossing PCIe.
+
+(1) Column-slab pipeline -- feature matrices wider than one L2-sized slab (Reddit shape: 602
+    columns = 4 x 128 + 90).  Column c of S^K X depends on column c of X only, and the
+    standardisation of utils.py:119 is per column, so every slab is an independent job:
+
+    in:    H2D CSR(A) | H2D X[:,s0] | H2D X[:,s1] | H2D X[:,s2] | ...
+    main:             | K1 K2 S plan | K3+std+K hops s0 | K3+std+K hops s1 | ...
+    out:                                               | D2H Y[:,s0]      | D2H Y[:,s1] | ...
+
+    The slab copies are strided 2-D DMA transfers (sgc_copy_2d) between the caller's row-major
+    pinned [N, F] matrix and padded device rows.  The slab width is the one the hop kernel tiles
+    with anyway (one slab of the gathered operand stays resident in L2).
+
+(2) Row-block pipeline -- narrow feature matrices (one slab): uploads as above, then the LAST hop is
+    launched per block of output rows (row-slice views of the same CSR arrays, the same kernel) and
+    block b is copied back while block b+1 is computed.
+"""
+import os
+
+import torch
+
+from . import _ffi
+from .features import col_stats, padded_rows, standardize_
+from .graph import L2_SLAB_BUDGET, SgcGraph, normalize_csr, require_cuda
+from .propagate import default_chunk, hop
+
+_copy_streams = {}
+
+
+def _copy_streams_for(dev):
+    s = _copy_streams.get(dev.index)
+    if s is None:
+        s = _copy_streams[dev.index] = (torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev))
+    return s
+
+
+def default_out_blocks():
+    """Row blocks of the last hop (SGC_B200_OUT_BLOCKS; 1 = one launch, then one D2H)."""
+    return max(1, int(os.environ.get("SGC_B200_OUT_BLOCKS", "8")))
+
+
+def row_blocks(graph, n_blocks):
+    """Row-slice views [(r0, r1, SgcGraph)] of `graph` with roughly equal numbers of stored entries
+    (not rows: power-law graphs), sharing its CSR arrays.  One small D2H read of the block
+    boundaries."""
+    n = graph.n_rows
+    n_blocks = max(1, min(int(n_blocks), n))
+    if n_blocks == 1:
+        return [(0, n, graph)]
+    targets = torch.arange(1, n_blocks, device=graph.device, dtype=torch.int64) * (graph.nnz // n_blocks)
+    cuts = torch.searchsorted(graph.row_ptr, targets).clamp_(0, n).cpu().tolist()
+    # 128-row alignment keeps each block a whole number of warps' worth of tasks
+    bounds = [0] + [min(n, (c + 127) // 128 * 128) for c in cuts] + [n]
+    out = []
+    for r0, r1 in zip(bounds[:-1], bounds[1:]):
+        if r1 <= r0:
+            continue
+        sub = SgcGraph(r1 - r0, graph.n_cols, graph.row_ptr[r0:r1 + 1], graph.col, graph.aval, graph.dinv,
+                       sval=graph.sval, dinv_rows=None if graph.dinv_rows is None else graph.dinv_rows[r0:r1])
+        out.append((r0, r1, sub))
+    return out
+
+
+def default_col_slab(n, f):
+    """Feature-slab width (floats) of the column pipeline: the widest slab the hop kernel is built
+    for whose N x width x 4-byte working set fits the L2 budget (spmm.cu: default_slab); 0 = the
+    matrix is one slab (or no slab fits L2) -> row-block schedule.  SGC_B200_COL_SLAB overrides."""
+    env = os.environ.get("SGC_B200_COL_SLAB")
+    if env is not None:
+        w = int(env)
+        return w if 0 < w < f else 0
+    for w in (256, 128, 64, 32):
+        if n * w * 4 <= L2_SLAB_BUDGET:
+            return w if w < f else 0
+    return 0
+
+
+def slab_widths(f, width):
+    """Column slabs of the pipeline, in processing order: full slabs of `width` floats, then the
+    remainder.  (Cutting the last slab further to shorten the un-overlapped tail was measured and
+    does not pay: narrow strided copies run at 2/3 of the PCIe rate, 24.9 vs 24.0 ms end to end.)"""
+    if not width or width >= f:
+        return [f]
+    widths = [width] * (f // width)
+    if f % width:
+        widths.append(f % width)
+    return widths
+
+
+def _host_csr(adj):
+    if isinstance(adj, tuple):
+        return adj
+    import numpy as np
+    import scipy.sparse as sp
+    m = adj.tocsr() if sp.issparse(adj) else sp.csr_matrix(adj)
+    return (m.shape[0], torch.from_numpy(np.ascontiguousarray(m.indptr, dtype=np.int64)),
+            torch.from_numpy(np.ascontiguousarray(m.indices, dtype=np.int32)),
+            torch.from_numpy(np.ascontiguousarray(m.data, dtype=np.float64)))
+
+
+def precompute_host(adj, features, degree, standardize=False, out=None, out_blocks=None, chunk=None,
+                    col_slab=None, trace=None):
+    """`sgc_precompute(features, aug_normalized_adjacency(adj), degree)` for HOST inputs, result
+    in host memory.
+
+    adj       scipy sparse matrix, or a tuple (n, row_ptr, col, val) of host tensors holding the
+              CSR of A (int64 / int32 / float64; pinned memory makes the copies asynchronous)
+    features  host fp32 tensor [N, F], contiguous (pinned for asynchronous copies)
+    degree    K >= 1
+    standardize   apply utils.py:119 ((x - mean) / std per column, unbiased std) before the hops
+    out       optional pinned fp32 [N, F] host tensor receiving the result
+    out_blocks / col_slab   schedule knobs (defaults: SGC_B200_OUT_BLOCKS, default_col_slab)
+    trace     optional list; receives (label, milliseconds since the call started) for the device-side
+              milestones of the schedule (CUDA events), for tools/e2e_sweep.py
+    Returns `out` (complete when the call returns)."""
+    dev = require_cuda()
+    degree = int(degree)
+    if degree < 1:
+        raise ValueError("degree must be >= 1")
+    n, rp_h, col_h, val_h = _host_csr(adj)
+    n = int(n)
+    if features.dim() != 2 or features.shape[0] != n or features.dtype != torch.float32 or features.is_cuda:
+        raise ValueError("features must be a host float32 [N, F] tensor with N = %d rows" % n)
+    features = features.contiguous()
+    f = int(features.shape[1])
+    if out is None:
+        out = torch.empty((n, f), dtype=torch.float32).pin_memory()
+    if tuple(out.shape) != (n, f) or out.dtype != torch.float32 or not out.is_contiguous() or out.is_cuda:
+        raise ValueError("out must be a contiguous float32 [N, F] host tensor")
+    chunk = default_chunk() if chunk is None else chunk
+    if isinstance(col_slab, (list, tuple)):            # explicit slab widths, in processing order
+        widths = [int(w) for w in col_slab]
+        if sum(widths) != f or any(w <= 0 or w % 4 for w in widths[:-1]):
+            raise ValueError("col_slab widths must be multiples of 4 floats summing to F")
+    else:
+        width = default_col_slab(n, f) if col_slab is None else (int(col_slab) if 0 < int(col_slab) < f else 0)
+        if width % 4:
+            raise ValueError("col_slab must be a multiple of 4 floats")
+        widths = slab_widths(f, width)
+
+    with torch.cuda.device(dev):
+        main = torch.cuda.current_stream()
+        c_in, c_out = _copy_streams_for(dev)
+        marks = []
+
+        def mark(label, stream):
+            if trace is not None:
+                e = torch.cuda.Event(enable_timing=True)
+                e.record(stream)
+                marks.append((label, e))
+
+        x = padded_rows(n, f, dev)
+        ld = x.stride(0)
+        c_in.wait_stream(main)
+        c_out.wait_stream(main)
+        mark("start", main)
+        starts = [sum(widths[:i]) for i in range(len(widths))]
+        slabs = [(c0, c0 + w) for c0, w in zip(starts, widths)]
+        by_cols = len(slabs) > 1
+        with torch.cuda.stream(c_in):
+            rp = rp_h.to(dev, non_blocking=True)
+            col = col_h.to(dev, non_blocking=True)
+            val = val_h.to(dev, non_blocking=True)
+            csr_up = torch.cuda.Event()
+            csr_up.record(c_in)
+            mark("csr up", c_in)
+            x_up = []
+            for c0, c1 in slabs:
+                if by_cols:
+                    _ffi.call("sgc_copy_2d", x.data_ptr() + 4 * c0, 4 * ld, features.data_ptr() + 4 * c0, 4 * f,
+                              4 * (c1 - c0), n, c_in.cuda_stream)
+                else:
+                    x.copy_(features, non_blocking=True)       # whole rows: one contiguous transfer
+                e = torch.cuda.Event()
+                e.record(c_in)
+                x_up.append(e)
+                mark("x[:, %d:%d] up" % (c0, c1), c_in)
+        for t in (rp, col, val):
+            t.record_stream(main)
+        x.record_stream(c_in)
+
+        # adjacency side, while the features are still on their way
+        main.wait_event(csr_up)
+        graph = normalize_csr(n, rp, col, val)
+        graph.values32()
+        if by_cols:
+            graph.plan(chunk)
+            blocks = None
+        else:
+            blocks = row_blocks(graph, default_out_blocks() if out_blocks is None else int(out_blocks))
+            if degree > 1:
+                graph.plan(chunk)
+            for _, _, sub in blocks:
+                sub.plan(chunk)
+        mark("normalised", main)
+        bufs = [padded_rows(n, f, dev) for _ in range(min(degree - 1, 2))]
+        # column slabs land in padded rows (aligned vector stores; the strided D2H drops the padding);
+        # whole-row blocks go back as contiguous pieces
+        y = padded_rows(n, f, dev) if by_cols else torch.empty((n, f), dtype=torch.float32, device=dev)
+        y.record_stream(c_out)
+
+        def back(r0, r1, c0, c1):
+            done = torch.cuda.Event()
+            done.record(main)
+            c_out.wait_event(done)
+            mark("y[%d:%d, %d:%d] computed" % (r0, r1, c0, c1), main)
+            if by_cols:
+                _ffi.call("sgc_copy_2d", out.data_ptr() + 4 * (r0 * f + c0), 4 * f,
+                          y.data_ptr() + 4 * (r0 * ld + c0), 4 * ld, 4 * (c1 - c0), r1 - r0, c_out.cuda_stream)
+            else:
+                with torch.cuda.stream(c_out):
+                    out[r0:r1].copy_(y[r0:r1], non_blocking=True)
+            mark("y[%d:%d, %d:%d] down" % (r0, r1, c0, c1), c_out)
+
+        for (c0, c1), up in zip(slabs, x_up):
+            main.wait_event(up)
+            cur = x[:, c0:c1]
+            if standardize:
+                mean, std = col_stats(cur)
+                standardize_(cur, mean, std)
+            for k in range(degree - 1):
+                nxt = bufs[k & 1][:, c0:c1]
+                hop(graph, cur, chunk=chunk, out=nxt)
+                cur = nxt
+            if blocks is None:
+                hop(graph, cur, chunk=chunk, out=y[:, c0:c1])
+                back(0, n, c0, c1)
+            else:
+                # last hop by row blocks, each block copied back while the next one is computed
+                for r0, r1, sub in blocks:
+                    hop(sub, cur, chunk=chunk, out=y[r0:r1, c0:c1])
+                    back(r0, r1, c0, c1)
+        main.wait_stream(c_out)
+        c_out.synchronize()
+        if trace is not None:
+            main.synchronize()
+            trace.extend((label, marks[0][1].elapsed_time(e)) for label, e in marks)
+    return out

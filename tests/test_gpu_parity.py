@@ -243,19 +243,25 @@ def test_hot_column_tags(dev, monkeypatch):
 
 
 def test_fused_norm_mode_is_bit_identical(dev, monkeypatch):
-    """SGC_B200_FUSED_NORM=1 (weights formed in the kernel from fp64 A+I values and D^-1/2) and the
-    default (fp32 S values written once by sgc_norm_build) give the same bits, split rows included."""
+    """SGC_B200_FUSED_NORM=1 (weights formed in the kernel from fp64 A+I values and D^-1/2; S is
+    never materialised) and the default (fp32 S values written once by sgc_norm_values at
+    normalisation time) give the same bits, split rows included."""
     import sgc_b200
-    s, graph = powerlaw_case(dev, scale=0.01, seed=9)
-    x = s["x"][:, :100].contiguous()
-    monkeypatch.setenv("SGC_B200_FUSED_NORM", "1")
-    assert graph.sval is None
-    a, _ = sgc_b200.sgc_precompute(x, graph, 2)
-    assert graph.sval is None                                      # nothing was materialised
-    monkeypatch.setenv("SGC_B200_FUSED_NORM", "0")
-    b, _ = sgc_b200.sgc_precompute(x, graph, 2)
-    assert graph.sval is not None
-    assert torch.equal(a, b)
+    x = None
+    outs = []
+    for mode in ("1", "0"):
+        monkeypatch.setenv("SGC_B200_FUSED_NORM", mode)
+        s, graph = powerlaw_case(dev, scale=0.01, seed=9)
+        assert (graph.sval is None) == (mode == "1")
+        x = s["x"][:, :100].contiguous()
+        y, _ = sgc_b200.sgc_precompute(x, graph, 2)
+        assert (graph.sval is None) == (mode == "1")               # fused mode materialises nothing
+        outs.append(y)
+    assert torch.equal(outs[0], outs[1])
+    # the general kernel (sgc_norm_build, used for views and row slices) writes the same fp32 values
+    sv = graph.sval
+    graph.sval = None
+    assert torch.equal(graph.values32(), sv)
 
 
 def test_fused_standardisation(dev):
@@ -298,6 +304,39 @@ def test_fused_standardisation(dev):
     assert torch.equal(feats2[np.arange(0, 50)], ((x - mean32) / std32)[:50])
     y3, _ = sgc_b200.sgc_precompute(feats2, graph, 2, chunk=0)         # idempotent: not applied twice
     assert torch.equal(y3, y2)
+
+
+@pytest.mark.parametrize("blocks,col_slab", [(1, None), (3, None), (8, None), (1, 32), (1, 64)])
+def test_precompute_host_pipeline(dev, blocks, col_slab):
+    """Host-to-host entry point (pipeline.precompute_host: overlapped H2D; column-slab pipeline or
+    row-blocked last hop with overlapped D2H) == sgc_precompute on device-resident inputs, bit for
+    bit, and == the oracle in exact mode; with and without the utils.py:119 standardisation;
+    K = 1, 2, 3."""
+    import sgc_b200
+    from oracle import spmm_oracle as so
+    s, graph = powerlaw_case(dev, scale=0.01, seed=7)
+    n = s["n"]
+    x = s["x"][:, :77].contiguous()
+    host = (n, s["row_ptr"].cpu().pin_memory(), s["col"].cpu().pin_memory(), s["val"].cpu().pin_memory())
+    x_host = x.cpu().pin_memory()
+    for k in (1, 2, 3):
+        want, _ = sgc_b200.sgc_precompute(sgc_b200.to_padded(x.clone()), graph, k)
+        got = sgc_b200.precompute_host(host, x_host, k, out_blocks=blocks, col_slab=col_slab)
+        assert not got.is_cuda and torch.equal(got, want.cpu())
+    # standardised, exact accumulation order: against the oracle on (x - mean) / std
+    mean32, std32 = sgc_b200.col_stats(x)
+    xs = ((x - mean32) / std32).cpu().numpy()
+    rp, col, val = graph.row_ptr.cpu().numpy(), graph.col.cpu().numpy(), graph.values32().cpu().numpy()
+    want2 = so.spmm_hop(rp, col, val, so.spmm_hop(rp, col, val, xs))
+    out = torch.empty((n, 77), dtype=torch.float32).pin_memory()
+    got2 = sgc_b200.precompute_host(host, x_host, 2, standardize=True, out=out, out_blocks=blocks, chunk=0,
+                                    col_slab=col_slab)
+    assert got2 is out and np.array_equal(out.numpy(), want2)
+    # scipy input (what the reference's loaders hold) takes the same path
+    import scipy.sparse as sp
+    a = sp.csr_matrix((host[3].numpy(), host[2].numpy(), host[1].numpy()), shape=(n, n))
+    got3 = sgc_b200.precompute_host(a, x_host, 2, standardize=True, out_blocks=blocks, chunk=0, col_slab=col_slab)
+    assert np.array_equal(got3.numpy(), want2)
 
 
 def test_downstream_accuracy_unchanged(dev):
