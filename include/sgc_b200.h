@@ -12,6 +12,8 @@
  *   utils.py:92-97          sgc_precompute (K x torch.spmm) -> sgc_spmm_plan_* / sgc_spmm_hop / sgc_precompute
  *   utils.py:118-119        Reddit feature standardisation   -> sgc_col_stats (+ fused into sgc_spmm_hop)
  *   utils.py:63,116-117     symmetrisation, induced sub-graph        -> sgc_sort_* / sgc_coo_reduce_* / sgc_subgraph_*
+ *   normalization.py:21-28, utils.py:20,74  row_normalize, sparse first hop  -> sgc_row_normalize, sgc_spmm_hop_sparse_x
+ *   downstream/TextSGC/utils.py:59-71,131-152  normalize_adj + precompute -> sgc_norm_values(order 1), sgc_gather_columns_dense, sgc_row_minmax, sgc_transpose_scale
  *   (no counterpart)        row-sharded multi-GPU propagation        -> sgc_symm_* / sgc_ipc_* / sgc_push_*
  *
  * Conventions
@@ -142,10 +144,13 @@ int32_t sgc_norm_build(int64_t n, const int64_t *row_ptr_d, const int32_t *col_d
 /* Fast path: values only, element-parallel.  s64_out_d / s32_out_d (either may be NULL) as in
  * sgc_norm_build; zero_flag_d[0] (device int64) <- 1 if any product is exactly zero, i.e. scipy
  * would prune the structure: the caller then runs sgc_norm_count + sgc_norm_build.  row_ptr_d[0]
- * must be 0 and row_ptr_d[n] == nnz. */
+ * must be 0 and row_ptr_d[n] == nnz.  order 0: (d_i * a_ij) * d_j, the association of
+ * normalization.py:12; order 1: (a_ij * d_j) * d_i, the association of TextSGC's normalize_adj
+ * (downstream/TextSGC/utils.py:66: adj.dot(D).transpose().dot(D).transpose()). */
 int32_t sgc_norm_values(int64_t n, int64_t nnz, const int64_t *row_ptr_d, const int32_t *col_d,
                         const double *aval_d, const double *dinv_rows_d, const double *dinv_d,
-                        double *s64_out_d, float *s32_out_d, int64_t *zero_flag_d, void *stream);
+                        int32_t order, double *s64_out_d, float *s32_out_d, int64_t *zero_flag_d,
+                        void *stream);
 /* CSR row pointers -> COO row indices (int64), and int32 -> int64 columns: the [2, nnz] index
  * tensor of utils.py:26-27.  idx_out_d has 2*nnz int64 (rows then cols). */
 int32_t sgc_csr_to_coo(int64_t n, const int64_t *row_ptr_d, const int32_t *col_d, int64_t nnz,
@@ -287,6 +292,41 @@ int32_t sgc_subgraph_count(int64_t m, const int64_t *idx_d, const int64_t *row_p
 int32_t sgc_subgraph_fill(int64_t m, const int64_t *idx_d, const int64_t *row_ptr_d, const int32_t *col_d,
                           const double *val_d, const int32_t *colmap_d, const int64_t *row_ptr_out_d,
                           int32_t *col_out_d, double *val_out_d, void *stream);
+
+/* ---- sparse feature matrices (normalization.py:21-28, utils.py:20,74) -----------
+ * sgc_row_normalize: val_out[p] = r_inv[row(p)] * val[p] with r = row sum accumulated sequentially in
+ *   stored order in the matrix dtype (fp32 when is_f64 == 0, as scipy does for the fp32 Planetoid
+ *   features), r_inv = 1/r, inf -> 0 (normalization.py:24-25).  val_out_d may alias val_d.
+ *   rinv_out_d (n entries of the same dtype) may be NULL.  zero_flag_d[0] <- 1 if some product is
+ *   exactly zero (scipy's CSR product drops those entries: the caller then compacts the structure).
+ * sgc_spmm_hop_sparse_x: Y = S X for X stored as canonical CSR (fp32): the first hop of
+ *   sgc_precompute on citation-style sparse features without densifying X; bit-identical to the dense
+ *   hop in its exact (chunk = 0) accumulation order.  Output row-major [n_rows, ldy], every column
+ *   of every row written.  f * 4 bytes must fit the shared-memory row budget (200 KB). */
+int32_t sgc_row_normalize(int64_t n, const int64_t *row_ptr_d, const void *val_d, int32_t is_f64,
+                          void *val_out_d, void *rinv_out_d, int64_t *zero_flag_d, void *stream);
+int32_t sgc_spmm_hop_sparse_x(int64_t n_rows, const int64_t *s_row_ptr_d, const int32_t *s_col_d,
+                              const float *s_val_d, const int64_t *x_row_ptr_d, const int32_t *x_col_d,
+                              const float *x_val_d, int32_t f, float *y_d, int64_t ldy, void *stream);
+
+/* ---- TextSGC precompute (downstream/TextSGC/utils.py:131-152) -------------------
+ *   train_feats = torch.spmm(adj, dense_adj[:, idx]).t(); min/max over documents; drop features
+ *   whose range is 0; (feats - train_min) / train_range
+ * sgc_gather_columns_dense: out_d[row, colmap_d[c]] = val_d[p] for every stored entry p = (row, c)
+ *   with colmap_d[c] >= 0 (colmap from sgc_subgraph_colmap): the dense N x m operand
+ *   dense_adj[:, idx] without ever forming the N x N dense matrix.  out_d must be zero-filled.
+ * sgc_row_minmax: per row of the hop output y_d [n, m]: min_d[r] = min_t y[r,t], range_d[r] =
+ *   max_t y[r,t] - min_d[r]  (fp32).
+ * sgc_transpose_scale: out_d[t, j] = (y[keep_d[j], t] - min_d[keep_d[j]]) / range_d[keep_d[j]] for
+ *   t < m, j < k; out_d is [m, ld_out] row-major.  One IEEE subtraction + division per element. */
+int32_t sgc_gather_columns_dense(int64_t n, int64_t nnz, const int64_t *row_ptr_d, const int32_t *col_d,
+                                 const float *val_d, const int32_t *colmap_d, float *out_d, int64_t ld,
+                                 void *stream);
+int32_t sgc_row_minmax(const float *y_d, int64_t n, int64_t m, int64_t ld, float *min_d, float *range_d,
+                       void *stream);
+int32_t sgc_transpose_scale(const float *y_d, int64_t m, int64_t ld, const int64_t *keep_d, int64_t k,
+                            const float *min_d, const float *range_d, float *out_d, int64_t ld_out,
+                            void *stream);
 
 /* ---- K5: row-sharded multi-GPU propagation (north_star (3); no counterpart in the reference) ---
  * One process per GPU.  Every rank owns a contiguous row range of S and keeps two full-height

@@ -51,7 +51,12 @@ SIGNATURES = {
     "sgc_csr_selfloop_build": (c_i32, [c_i64, c_i64, c_p, c_p, c_p, c_p, c_p, c_p, c_p]),
     "sgc_csr_augment_count": (c_i32, [c_i64, c_i64, c_i64, c_i64, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_sz, c_p]),
     "sgc_csr_augment_build": (c_i32, [c_i64, c_i64, c_i64, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p]),
-    "sgc_norm_values": (c_i32, [c_i64, c_i64, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p]),
+    "sgc_norm_values": (c_i32, [c_i64, c_i64, c_p, c_p, c_p, c_p, c_p, c_i32, c_p, c_p, c_p, c_p]),
+    "sgc_row_normalize": (c_i32, [c_i64, c_p, c_p, c_i32, c_p, c_p, c_p, c_p]),
+    "sgc_spmm_hop_sparse_x": (c_i32, [c_i64, c_p, c_p, c_p, c_p, c_p, c_p, c_i32, c_p, c_i64, c_p]),
+    "sgc_gather_columns_dense": (c_i32, [c_i64, c_i64, c_p, c_p, c_p, c_p, c_p, c_i64, c_p]),
+    "sgc_row_minmax": (c_i32, [c_p, c_i64, c_i64, c_i64, c_p, c_p, c_p]),
+    "sgc_transpose_scale": (c_i32, [c_p, c_i64, c_i64, c_p, c_i64, c_p, c_p, c_p, c_i64, c_p]),
     "sgc_degree_inv_sqrt": (c_i32, [c_i64, c_p, c_p, c_p, c_p, c_p]),
     "sgc_norm_count": (c_i32, [c_i64, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_sz, c_p]),
     "sgc_norm_build": (c_i32, [c_i64, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p]),

@@ -243,8 +243,8 @@ degree_warp_kernel(int64_t n, const int64_t *__restrict__ row_ptr, const double 
 __global__ void __launch_bounds__(EP_THREADS)
 norm_values_kernel(int64_t n, int64_t nnz, const int64_t *__restrict__ row_ptr, const int32_t *__restrict__ col,
                    const double *__restrict__ aval, const double *__restrict__ dinv_rows,
-                   const double *__restrict__ dinv, double *__restrict__ s64_out, float *__restrict__ s32_out,
-                   int64_t *__restrict__ zero_flag)
+                   const double *__restrict__ dinv, int order, double *__restrict__ s64_out,
+                   float *__restrict__ s32_out, int64_t *__restrict__ zero_flag)
 {
     __shared__ int32_t srp[EP_ROWS + 1];
     const RowTile t = tile_setup(row_ptr, n, nnz, srp);
@@ -255,15 +255,35 @@ norm_values_kernel(int64_t n, int64_t nnz, const int64_t *__restrict__ row_ptr, 
         bool first;
         const int64_t row = tile_row_of(t, srp, row_ptr, p, &first);
         const double di = dinv_rows[row], dj = dinv[c];
-        // scipy's csr_matmat drops products that are exactly zero (first D*Ahat, then (D*Ahat)*D)
-        const double left = __dmul_rn(di, a);
-        const double s = __dmul_rn(left, dj);
+        // scipy's csr_matmat drops products that are exactly zero (first D*Ahat, then (D*Ahat)*D;
+        // TextSGC's normalize_adj multiplies the column factor first: (Ahat*D)^T*D)
+        const double left = order == 0 ? __dmul_rn(di, a) : __dmul_rn(a, dj);
+        const double s = __dmul_rn(left, order == 0 ? dj : di);
         if (!(left != 0.0) || !(s != 0.0)) zero = true;
         if (s64_out) s64_out[p] = s;
         if (s32_out) s32_out[p] = __double2float_rn(s);                 // utils.py:25 astype(float32)
     }
     if (__any_sync(0xffffffffu, zero) && (threadIdx.x & 31) == 0)
         atomicOr(reinterpret_cast<unsigned long long *>(zero_flag), 1ull);
+}
+
+// Dense copy of selected columns of a CSR matrix: out[row, colmap[c]] = val for every stored entry
+// whose column is selected (colmap[c] >= 0).  out must be zero-filled.  (TextSGC feeds
+// dense_adj[:, idx] to torch.spmm, downstream/TextSGC/utils.py:135.)
+__global__ void __launch_bounds__(EP_THREADS)
+gather_columns_kernel(int64_t n, int64_t nnz, const int64_t *__restrict__ row_ptr, const int32_t *__restrict__ col,
+                      const float *__restrict__ val, const int32_t *__restrict__ colmap, float *__restrict__ out,
+                      int64_t ld)
+{
+    __shared__ int32_t srp[EP_ROWS + 1];
+    const RowTile t = tile_setup(row_ptr, n, nnz, srp);
+    for (int64_t p = t.p0 + threadIdx.x; p < t.p1; p += EP_THREADS) {
+        const int32_t k = colmap[col[p]];
+        if (k < 0) continue;
+        bool first;
+        const int64_t row = tile_row_of(t, srp, row_ptr, p, &first);
+        out[row * ld + k] = val[p];
+    }
 }
 
 }  // namespace sgc
@@ -335,15 +355,30 @@ int32_t sgc_degree_inv_sqrt(int64_t n, const int64_t *row_ptr_d, const double *a
 
 int32_t sgc_norm_values(int64_t n, int64_t nnz, const int64_t *row_ptr_d, const int32_t *col_d,
                         const double *aval_d, const double *dinv_rows_d, const double *dinv_d,
-                        double *s64_out_d, float *s32_out_d, int64_t *zero_flag_d, void *stream)
+                        int32_t order, double *s64_out_d, float *s32_out_d, int64_t *zero_flag_d,
+                        void *stream)
 {
+    SGC_REQUIRE(order == 0 || order == 1, "norm_values: order must be 0 or 1");
     SGC_REQUIRE(n >= 0 && nnz >= 0 && row_ptr_d && dinv_rows_d && dinv_d && zero_flag_d, "norm_values: bad arguments");
     cudaStream_t s = as_stream(stream);
     SGC_CUDA_TRY(cudaMemsetAsync(zero_flag_d, 0, sizeof(int64_t), s));
     if (n == 0 || nnz == 0) return SGC_OK;
     SGC_REQUIRE(col_d && aval_d, "norm_values: null arrays");
     norm_values_kernel<<<(unsigned)ceil_div(nnz, EP_TILE), EP_THREADS, 0, s>>>(
-        n, nnz, row_ptr_d, col_d, aval_d, dinv_rows_d, dinv_d, s64_out_d, s32_out_d, zero_flag_d);
+        n, nnz, row_ptr_d, col_d, aval_d, dinv_rows_d, dinv_d, order, s64_out_d, s32_out_d, zero_flag_d);
+    SGC_LAUNCH_CHECK();
+    return SGC_OK;
+}
+
+int32_t sgc_gather_columns_dense(int64_t n, int64_t nnz, const int64_t *row_ptr_d, const int32_t *col_d,
+                                 const float *val_d, const int32_t *colmap_d, float *out_d, int64_t ld,
+                                 void *stream)
+{
+    SGC_REQUIRE(n >= 0 && nnz >= 0 && row_ptr_d && colmap_d, "gather_columns_dense: bad arguments");
+    if (n == 0 || nnz == 0) return SGC_OK;
+    SGC_REQUIRE(col_d && val_d && out_d && ld >= 1, "gather_columns_dense: null arrays");
+    gather_columns_kernel<<<(unsigned)ceil_div(nnz, EP_TILE), EP_THREADS, 0, as_stream(stream)>>>(
+        n, nnz, row_ptr_d, col_d, val_d, colmap_d, out_d, ld);
     SGC_LAUNCH_CHECK();
     return SGC_OK;
 }

@@ -50,8 +50,11 @@ class SgcGraph(object):
 
     is_sparse = True
 
-    def __init__(self, n_rows, n_cols, row_ptr, col, aval, dinv, rowsum=None, sval=None, dinv_rows=None):
+    def __init__(self, n_rows, n_cols, row_ptr, col, aval, dinv, rowsum=None, sval=None, dinv_rows=None, order=0):
         self.n_rows, self.n_cols = int(n_rows), int(n_cols)
+        # association of the value product: 0 = (d_i*a)*d_j (normalization.py:12), 1 = (a*d_j)*d_i
+        # (TextSGC's normalize_adj, downstream/TextSGC/utils.py:66)
+        self.order = int(order)
         self.row_ptr, self.col, self.aval, self.dinv, self.rowsum = row_ptr, col, aval, dinv, rowsum
         self.dinv_rows = dinv if dinv_rows is None else dinv_rows     # differs for a row slice only
         self.sval = sval                      # fp32 values of S when materialised (or given)
@@ -83,7 +86,16 @@ class SgcGraph(object):
 
     @property
     def fused(self):
-        return self.aval is not None and self.dinv is not None
+        """True when the hop kernel may form the weights itself from aval and dinv (order 0 only:
+        the kernel multiplies in the order of normalization.py:12)."""
+        return self.aval is not None and self.dinv is not None and self.order == 0
+
+    def _norm_values(self, s64, s32):
+        zero = torch.empty(1, dtype=torch.int64, device=self.device)
+        with torch.cuda.device(self.device):
+            _ffi.call("sgc_norm_values", self.n_rows, self.nnz, _ffi.ptr(self.row_ptr), _ffi.ptr(self.col),
+                      _ffi.ptr(self.aval), _ffi.ptr(self.dinv_rows), _ffi.ptr(self.dinv), self.order,
+                      _ffi.ptr(s64), _ffi.ptr(s32), _ffi.ptr(zero), stream_ptr())
 
     # -- plan cache --------------------------------------------------------------------------
     def plan(self, chunk):
@@ -106,6 +118,9 @@ class SgcGraph(object):
     # -- views -------------------------------------------------------------------------------
     def values32(self):
         """fp32 values of S: fp32((d_i*a_ij)*d_j), the single rounding of utils.py:25."""
+        if self.sval is None and self.order != 0:
+            self.sval = torch.empty(self.nnz, dtype=torch.float32, device=self.device)
+            self._norm_values(None, self.sval)
         if self.sval is None:
             self.sval = torch.empty(self.nnz, dtype=torch.float32, device=self.device)
             with torch.cuda.device(self.device):
@@ -117,6 +132,9 @@ class SgcGraph(object):
     def values64(self):
         """fp64 values of S as normalization.py:12 returns them."""
         out = torch.empty(self.nnz, dtype=torch.float64, device=self.device)
+        if self.order != 0:
+            self._norm_values(out, None)
+            return out
         with torch.cuda.device(self.device):
             _ffi.call("sgc_norm_build", self.n_rows, _ffi.ptr(self.row_ptr), _ffi.ptr(self.col),
                       _ffi.ptr(self.aval), _ffi.ptr(self.dinv_rows), _ffi.ptr(self.dinv),
@@ -293,7 +311,8 @@ def augment_csr(n_rows, n_cols, row_offset, row_ptr, col, val):
     return rp_aug, col_aug, aval, rowsum, dinv
 
 
-def finish_normalization(n_rows, n_cols, rp_aug, col_aug, aval, rowsum, dinv_rows, dinv_cols, materialize=None):
+def finish_normalization(n_rows, n_cols, rp_aug, col_aug, aval, rowsum, dinv_rows, dinv_cols, materialize=None,
+                         order=0):
     """Structure of S after scipy's zero-product pruning (normalization.py:12; it only differs
     from A + I when some D^-1/2 entry is zero) -> `SgcGraph`.  dinv_rows: D^-1/2 of the slice's
     rows; dinv_cols: D^-1/2 of all n_cols columns."""
@@ -302,7 +321,7 @@ def finish_normalization(n_rows, n_cols, rp_aug, col_aug, aval, rowsum, dinv_row
     n = int(n_rows)
     if materialize is None:
         import os
-        materialize = os.environ.get("SGC_B200_FUSED_NORM", "0") != "1"
+        materialize = os.environ.get("SGC_B200_FUSED_NORM", "0") != "1" or order != 0
     with torch.cuda.device(dev):
         s = stream_ptr()
         # fast path: the fp32 values of S in one element-parallel pass, which also reports whether
@@ -311,7 +330,10 @@ def finish_normalization(n_rows, n_cols, rp_aug, col_aug, aval, rowsum, dinv_row
         sval = torch.empty(nnz, dtype=torch.float32, device=dev) if materialize else None
         zero = torch.empty(1, dtype=torch.int64, device=dev)
         _ffi.call("sgc_norm_values", n, nnz, _ffi.ptr(rp_aug), _ffi.ptr(col_aug), _ffi.ptr(aval),
-                  _ffi.ptr(dinv_rows), _ffi.ptr(dinv_cols), None, _ffi.ptr(sval), _ffi.ptr(zero), s)
+                  _ffi.ptr(dinv_rows), _ffi.ptr(dinv_cols), int(order), None, _ffi.ptr(sval), _ffi.ptr(zero), s)
+        if int(zero.item()) != 0 and order != 0:
+            raise _ffi.SgcError("normalize_adj: a zero degree prunes the structure; only the association of "
+                                "normalization.py:12 implements scipy's pruning")
         if int(zero.item()) != 0:
             sval = None
             scan_ws = _ws(lib.sgc_scan_workspace_bytes(n + 1), dev)
@@ -328,16 +350,18 @@ def finish_normalization(n_rows, n_cols, rp_aug, col_aug, aval, rowsum, dinv_row
                           _ffi.ptr(dinv_rows), _ffi.ptr(dinv_cols), _ffi.ptr(rp_s), _ffi.ptr(col_s),
                           _ffi.ptr(aval_s), None, None, s)
                 rp_aug, col_aug, aval = rp_s, col_s, aval_s
-    return SgcGraph(n, int(n_cols), rp_aug, col_aug, aval, dinv_cols, rowsum=rowsum, dinv_rows=dinv_rows, sval=sval)
+    return SgcGraph(n, int(n_cols), rp_aug, col_aug, aval, dinv_cols, rowsum=rowsum, dinv_rows=dinv_rows, sval=sval,
+                    order=order)
 
 
-def normalize_csr(n, row_ptr, col, val):
+def normalize_csr(n, row_ptr, col, val, order=0):
     """``aug_normalized_adjacency`` on device CSR arrays (normalization.py:5-12).
 
     row_ptr int64 [n+1], col int32 [nnz], val float64 [nnz], all on one CUDA device; any stored
-    order (non-canonical input is canonicalised first).  Returns an `SgcGraph`."""
+    order (non-canonical input is canonicalised first).  Returns an `SgcGraph`.  order=1 multiplies
+    in the order of TextSGC's normalize_adj (see `SgcGraph.order`)."""
     rp_aug, col_aug, aval, rowsum, dinv = augment_csr(n, n, 0, row_ptr, col, val)
-    return finish_normalization(n, n, rp_aug, col_aug, aval, rowsum, dinv, dinv)
+    return finish_normalization(n, n, rp_aug, col_aug, aval, rowsum, dinv, dinv, order=order)
 
 
 def upload_csr(adj, device=None):
@@ -360,12 +384,12 @@ def upload_csr(adj, device=None):
     return m.shape, row_ptr, col, val
 
 
-def from_scipy(adj, device=None):
+def from_scipy(adj, device=None, order=0):
     """normalization.aug_normalized_adjacency on a scipy matrix: upload, then K1/K2 on the GPU."""
     shape, row_ptr, col, val = upload_csr(adj, device)
     if shape[0] != shape[1]:
         raise ValueError("adjacency must be square, got %s" % (shape,))
-    return normalize_csr(shape[0], row_ptr, col, val)
+    return normalize_csr(shape[0], row_ptr, col, val, order=order)
 
 
 def from_torch_sparse(t):

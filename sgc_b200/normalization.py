@@ -5,9 +5,6 @@ GPU kernels.
     fetch_normalization(type)       /root/reference/normalization.py:14-19
     row_normalize(mx)               /root/reference/normalization.py:21-28
 """
-import numpy as np
-import scipy.sparse as sp
-
 from .graph import SgcGraph, from_scipy
 
 
@@ -31,12 +28,9 @@ def fetch_normalization(type):
 
 
 def row_normalize(mx):
-    """Feature rows divided by their sum (inf -> 0).  Host-side scipy, as in the reference: the
-    citation feature matrices are a few MB and are outside the propagation path; the dense GPU
-    hand-off happens in utils.load_citation."""
-    mx = sp.csr_matrix(mx) if not sp.issparse(mx) else mx
-    total = np.asarray(mx.sum(1)).ravel()
-    with np.errstate(divide="ignore"):
-        inv = np.power(total, -1)
-    inv[np.isinf(inv)] = 0.0
-    return sp.diags(inv).dot(mx)
+    """Feature rows divided by their sum, inf -> 0 (normalization.py:21-28), on the GPU
+    (sgc_row_normalize).  Takes the scipy sparse matrix the reference takes; returns a
+    `SparseFeatures` (GPU CSR) that answers ``.todense()`` / ``.tocsr()`` like the scipy matrix the
+    reference returns."""
+    from .sparse_features import row_normalize as _row_normalize
+    return _row_normalize(mx)

@@ -160,10 +160,21 @@ def propagate(adj, x, degree, mean=None, std=None, chunk=None, slab=None, hints=
         return x
     if g.n_rows != g.n_cols:
         raise ValueError("K-hop propagation needs a square adjacency, got %s" % (g.shape,))
+    from .sparse_features import hop_sparse_x, sparse_origin
+    sf = sparse_origin(x) if mean is None else None
     x = _check_features(g, x)
     n, f = int(x.shape[0]), int(x.shape[1])
     if mean is not None:
         mean, std = mean.to(dev, torch.float32).contiguous(), std.to(dev, torch.float32).contiguous()
+    if sf is not None and f * 4 <= 200 * 1024 and n > 0 and f > 0:
+        # citation-style sparse features: the first hop accumulates the stored entries
+        # of X only -- same per-element order as the dense kernel's exact mode
+        with torch.cuda.device(dev):
+            if degree == 1:
+                y = torch.empty((n, f), dtype=torch.float32, device=dev)
+                return hop_sparse_x(g, sf, out=y)
+            first = hop_sparse_x(g, sf)
+        return propagate(g, first, degree - 1, chunk=chunk, slab=slab, hints=hints)
     with torch.cuda.device(dev):
         y = torch.empty((n, f), dtype=torch.float32, device=dev)
         if f == 0 or n == 0:

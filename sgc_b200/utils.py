@@ -110,8 +110,10 @@ def load_citation(dataset_str="cora", normalization="AugNormAdj", cuda=True):
     adj, features = preprocess_citation(adj, features, normalization)   # adjacency: GPU kernels
 
     n_train = len(parts["y"])
-    # dense fp32 features in padded device storage (row stride a multiple of 8 floats)
-    features = to_padded(torch.from_numpy(np.asarray(features.todense(), dtype=np.float32)), dev)
+    # dense fp32 features in padded device storage (row stride a multiple of 8 floats), scattered on
+    # the GPU from the row-normalised CSR; the tensor keeps a handle on that CSR so that the first
+    # hop of sgc_precompute runs on the stored entries only (sparse_features.py)
+    features = features.to_dense_padded()
     labels = torch.from_numpy(labels).long().max(dim=1)[1].to(dev)
     idx_train = torch.arange(n_train, dtype=torch.long, device=dev)
     idx_val = torch.arange(n_train, n_train + 500, dtype=torch.long, device=dev)

@@ -16,6 +16,7 @@ What is recorded (all produced by reference code; nothing here re-implements it)
     negative row sums, unsorted/duplicate entries, asymmetric weighted input -> reference outputs.
   * a weighted asymmetric real-world block (TextSGC covid PMI/TF-IDF graph, induced sub-matrix on
     the 1800 busiest rows + 1200 random rows).
+  * the TextSGC precompute (downstream/TextSGC/utils.py: preprocess_adj, sgc_precompute) on that block.
 """
 import hashlib
 import os
@@ -218,9 +219,56 @@ def textsgc_block():
     np.savez_compressed(os.path.join(HERE, "textsgc_block.npz"), **out)
 
 
+def textsgc_precompute():
+    """downstream/TextSGC/utils.py (imported unmodified; its dead `eigsh` import no longer exists in
+    this scipy and is stubbed, `.cuda()` is made a no-op because this container has no GPU):
+    preprocess_adj -> sparse_to_torch_sparse / sparse_to_torch_dense -> sgc_precompute on the same
+    covid PMI/TF-IDF block, with random disjoint train/val/test column sets."""
+    import importlib.util
+    import types
+    blk = np.load(os.path.join(HERE, "textsgc_block.npz"))
+    n = blk["adj_indptr"].size - 1
+    adj = sp.csr_matrix((blk["adj_data"], blk["adj_indices"], blk["adj_indptr"]), shape=(n, n))
+    stub = types.ModuleType("scipy.sparse.linalg.eigen.arpack")
+    stub.eigsh = None
+    sys.modules.setdefault("scipy.sparse.linalg.eigen", types.ModuleType("scipy.sparse.linalg.eigen"))
+    sys.modules["scipy.sparse.linalg.eigen.arpack"] = stub
+    spec = importlib.util.spec_from_file_location("textsgc_utils", os.path.join(REF, "downstream/TextSGC/utils.py"))
+    T = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(T)
+    adj32 = adj.astype(np.float32)                                  # load_corpus: utils.py:53
+    sp_adj = T.preprocess_adj(adj32)                                # utils.py:54
+    t_adj = T.sparse_to_torch_sparse(sp_adj, device="cpu")          # train.py:49
+    dense = T.sparse_to_torch_dense(sp_adj, device="cpu")           # train.py:105
+    rng = np.random.RandomState(11)
+    perm = rng.permutation(n)
+    index_dict = {"train": np.sort(perm[:300]).tolist(), "val": np.sort(perm[300:380]).tolist(),
+                  "test": np.sort(perm[380:500]).tolist()}
+    orig_cuda = torch.Tensor.cuda
+    torch.Tensor.cuda = lambda self, *a, **k: self
+    try:
+        feat_dict, _ = T.sgc_precompute(t_adj, dense, 1, index_dict)    # train.py:106
+    finally:
+        torch.Tensor.cuda = orig_cuda
+    S = sp_adj.tocoo()
+    out = {}
+    out.update(csr_parts(adj32.astype(np.float64), "adj"))
+    out["S_row"], out["S_col"], out["S_data64"] = S.row.astype(np.int64), S.col.astype(np.int64), S.data
+    for ph in ("train", "val", "test"):
+        a = feat_dict[ph].numpy()
+        out["idx_" + ph] = np.asarray(index_dict[ph], dtype=np.int64)
+        out["feats_%s_shape" % ph] = np.asarray(a.shape, dtype=np.int64)
+        out["feats_%s_sha" % ph] = sha(a)
+        out["feats_%s_head" % ph] = a[:12].copy()
+        out["feats_%s_sum" % ph] = np.float64(a.astype(np.float64).sum())
+    print("textsgc precompute", {ph: tuple(feat_dict[ph].shape) for ph in feat_dict})
+    np.savez_compressed(os.path.join(HERE, "textsgc_precompute.npz"), **out)
+
+
 if __name__ == "__main__":
     citation("cora", 100)
     citation("citeseer", 150)
     pubmed()
     edge_cases()
     textsgc_block()
+    textsgc_precompute()

@@ -163,19 +163,17 @@ def test_planetoid_adjacency_matches_reference_loader():
         assert np.array_equal(adj.data.astype(np.float64), g["adj_data"])
 
 
-def test_row_normalize_matches_golden():
+def test_row_normalize_has_no_cpu_path():
+    """row_normalize (normalization.py:21-28) runs on the GPU (tests/test_gpu_sparse_features.py checks
+    it against the golden vectors); without a device it raises instead of falling back to scipy."""
     import scipy.sparse as sp
-    from conftest import load_golden
+    import torch
     import normalization as mine
-    for ds, f in (("cora", 1433), ("citeseer", 3703)):
-        g = load_golden(ds)
-        n = g["featraw_indptr"].size - 1
-        raw = sp.csr_matrix((g["featraw_data"], g["featraw_indices"], g["featraw_indptr"]), shape=(n, f))
-        out = sp.csr_matrix(mine.row_normalize(raw))
-        out.sort_indices()
-        out.eliminate_zeros()
-        assert np.array_equal(out.indices, g["featnorm_indices"])
-        assert np.array_equal(out.data.astype(np.float32), g["featnorm_data"].astype(np.float32))
+    from sgc_b200 import _ffi
+    if torch.cuda.is_available():
+        pytest.skip("CPU-only check")
+    with pytest.raises(_ffi.SgcError):
+        mine.row_normalize(sp.identity(4, format="csr", dtype=np.float32))
 
 
 def test_standardized_features_semantics():
