@@ -403,6 +403,10 @@ def run_e2e(args, s, name, k, nnz_s, dev):
         sgc_b200.precompute_host((n, host["row_ptr"], host["col"], host["val"]), host["x"], k,
                                  standardize=(name == "reddit"), out=out_host)
 
+    widths = sgc_b200.pipeline.slab_widths(f, sgc_b200.pipeline.default_col_slab(n, f))
+    schedule = ("column slabs of %s floats, strided 2-D DMA copies" % "+".join(str(w) for w in widths)
+                if len(widths) > 1 else
+                "one contiguous copy; last hop in %d row blocks" % sgc_b200.pipeline.default_out_blocks())
     steps = max(2, min(args.steps, 5))
     step()
     t0 = time.perf_counter()
@@ -411,10 +415,10 @@ def run_e2e(args, s, name, k, nnz_s, dev):
     secs = (time.perf_counter() - t0) / steps
     return {"value": k * nnz_s * f / secs, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
             "d2h_bytes_per_step": int(d2h), "ms_per_step": secs * 1e3, "steps": steps,
-            "path": "sgc_b200.precompute_host: pinned host CSR(A)+X -> H2D -> aug_normalized_adjacency (K1,K2, "
-                    "overlapped with the upload of X) -> col_stats + standardise (K3) -> K hops (last hop in %d "
-                    "row blocks, each copied back while the next is computed) -> pinned host result"
-                    % sgc_b200.pipeline.default_out_blocks()}
+            "path": "sgc_b200.precompute_host: pinned host CSR(A)+X -> H2D (CSR first; X in %s) -> "
+                    "aug_normalized_adjacency (K1,K2, overlapped with the upload of X) -> per slab: col_stats + "
+                    "standardise (K3), K hops, strided D2H into the pinned host result while the next slab is "
+                    "uploaded and computed" % schedule}
 
 
 def main():

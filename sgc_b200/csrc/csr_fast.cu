@@ -197,8 +197,9 @@ aug_append_kernel(int64_t n, int64_t doff, const int32_t *__restrict__ info, con
 }
 
 // One warp per 32 consecutive rows.  Rows of at most SHORT entries are summed by their own lane;
-// longer rows by the whole warp, one after another: 32 entries per coalesced load, added in stored
-// order through a shuffle chain (all lanes carry the same running sum), next batch prefetched.
+// longer rows by the whole warp, one after another: 32 entries per coalesced load; integer-valued rows
+// are reduced in parallel (exact, see below), real-valued rows in stored order through a shuffle
+// chain (all lanes carry the same running sum), next batch prefetched.
 __global__ void __launch_bounds__(256)
 degree_warp_kernel(int64_t n, const int64_t *__restrict__ row_ptr, const double *__restrict__ aval,
                    double *__restrict__ rowsum, double *__restrict__ dinv)
@@ -218,17 +219,36 @@ degree_warp_kernel(int64_t n, const int64_t *__restrict__ row_ptr, const double 
             const int src = __ffs(todo) - 1;
             todo &= todo - 1;
             const int64_t rb = __shfl_sync(0xffffffffu, b, src), re = __shfl_sync(0xffffffffu, e, src);
+            // Exact shortcut: if every entry of the row is an integer of magnitude <= 2^20 (binary and
+            // count-weighted graphs: every BASELINE shape), all partial sums of fewer than 2^31 of them
+            // are exact in fp64, so ANY summation order gives the bits of the sequential one -- the
+            // lanes sum strided pieces with independent loads and combine by a tree.
+            double part = 0.0;
+            bool ints = true;
+            for (int64_t q = rb + lane; q < re; q += 32) {
+                const double v = aval[q];
+                ints &= (v == rint(v)) && (fabs(v) <= 1048576.0);
+                part += v;
+            }
             double acc = 0.0;
-            double nxt = (rb + lane < re) ? aval[rb + lane] : 0.0;
-            for (int64_t q = rb; q < re; q += 32) {
-                const double cur = nxt;
-                if (q + 32 < re) nxt = (q + 32 + lane < re) ? aval[q + 32 + lane] : 0.0;
-                const int cnt = (re - q < 32) ? (int)(re - q) : 32;
-                if (cnt == 32) {
+            if (__all_sync(0xffffffffu, ints)) {
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) acc = __dadd_rn(acc, __shfl_sync(0xffffffffu, cur, j));
-                } else {
-                    for (int j = 0; j < cnt; ++j) acc = __dadd_rn(acc, __shfl_sync(0xffffffffu, cur, j));
+                for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+                acc = part;
+            } else {
+                // real-valued weights (TextSGC's PMI / TF-IDF graph): stored order, through a shuffle
+                // chain; the row was just read, so these loads hit L1 / L2
+                double nxt = (rb + lane < re) ? aval[rb + lane] : 0.0;
+                for (int64_t q = rb; q < re; q += 32) {
+                    const double cur = nxt;
+                    if (q + 32 < re) nxt = (q + 32 + lane < re) ? aval[q + 32 + lane] : 0.0;
+                    const int cnt = (re - q < 32) ? (int)(re - q) : 32;
+                    if (cnt == 32) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) acc = __dadd_rn(acc, __shfl_sync(0xffffffffu, cur, j));
+                    } else {
+                        for (int j = 0; j < cnt; ++j) acc = __dadd_rn(acc, __shfl_sync(0xffffffffu, cur, j));
+                    }
                 }
             }
             if (lane == src) r = acc;
