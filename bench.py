@@ -225,6 +225,7 @@ def run_own(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # NCCL's banner / logs off stdout: ONE JSON line
         dist.init_process_group("nccl", device_id=dev)
     if world > 1:
         from sgc_b200 import dist as sgc_dist

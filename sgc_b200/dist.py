@@ -484,17 +484,18 @@ def run_feature_sharded_workload(name, args, rank, world, dev, B, with_e2e=True,
         host["x"] = x_raw_local.cpu().pin_memory()
         out_host = torch.empty((n, c1 - c0), dtype=torch.float32).pin_memory()
 
+        from .pipeline import precompute_host
+        host_csr = (n, host["row_ptr"], host["col"], host["val"])
+        # one node, one copy of the adjacency in host memory: every rank uploads 1/P of it and NVLink
+        # replicates it (SGC_B200_SHARED_CSR=0: every rank uploads all of it)
+        shared_csr = os.environ.get("SGC_B200_SHARED_CSR", "1") != "0" and \
+            all(b > a for a, b in partition_features(f, world))       # the all-gather needs every rank
+
         def e2e_step():
-            g2 = normalize_csr(n, host["row_ptr"].to(dev, non_blocking=True), host["col"].to(dev, non_blocking=True),
-                               host["val"].to(dev, non_blocking=True))
-            xl = to_padded(host["x"], dev)
-            feats = xl
-            if shape["scaled"]:
-                m2, s2 = col_stats(xl)                     # per column: local to this rank's block
-                feats = StandardizedFeatures(xl, m2, s2)
-            y, _ = sgc_precompute(feats, g2, k)
-            out_host.copy_(y, non_blocking=True)
-            torch.cuda.synchronize()
+            # this rank's column block through the pipelined host-to-host path (pipeline.py): CSR up,
+            # K1/K2 under the upload of X, per slab K3 + hops + strided D2H
+            precompute_host(host_csr, host["x"], k, standardize=bool(shape["scaled"]), out=out_host,
+                            group=dist.group.WORLD if shared_csr else None)
 
         e2e_step()
         dist.barrier()
@@ -505,11 +506,17 @@ def run_feature_sharded_workload(name, args, rank, world, dev, B, with_e2e=True,
         dist.barrier()
         e2e_s = torch.tensor([(time.perf_counter() - t0) / e2e_steps], dtype=torch.float64, device=dev)
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
-        h2d = torch.tensor([sum(t.numel() * t.element_size() for t in host.values())], dtype=torch.int64, device=dev)
+        mine = sum(t.numel() * t.element_size() for t in host.values())
+        if shared_csr:                                   # col / val: 1/P per rank, the rest over NVLink
+            mine -= (host["col"].numel() * 4 + host["val"].numel() * 8) * (world - 1) // world
+        h2d = torch.tensor([mine], dtype=torch.int64, device=dev)
         dist.all_reduce(h2d)
         out["e2e"] = {"value": k * nnz * f / float(e2e_s.item()), "unit": B["UNIT"],
                       "h2d_bytes_per_step": int(h2d.item()), "d2h_bytes_per_step": int(n * f * 4),
-                      "ms_per_step": float(e2e_s.item()) * 1e3}
+                      "ms_per_step": float(e2e_s.item()) * 1e3,
+                      "path": "per rank: sgc_b200.precompute_host on its column block (pipeline.py); adjacency "
+                              + ("uploaded once per node (1/P per rank over its own PCIe link, NCCL all-gather "
+                                 "over NVLink)" if shared_csr else "uploaded by every rank")}
     elif with_e2e:
         dist.barrier(); dist.barrier()
         z = torch.zeros(1, dtype=torch.float64, device=dev); dist.all_reduce(z, op=dist.ReduceOp.MAX)

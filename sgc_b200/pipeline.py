@@ -112,8 +112,31 @@ def _host_csr(adj):
             torch.from_numpy(np.ascontiguousarray(m.data, dtype=np.float64)))
 
 
+def _upload_csr_shared(rp_h, col_h, val_h, dev, group):
+    """CSR arrays of a host-resident adjacency onto every GPU of `group` when all ranks need the whole
+    matrix (feature-sharded propagation): each rank pulls 1/P of `col` / `val` over its own PCIe link
+    and an NCCL all-gather over NVLink assembles the full arrays on every GPU -- the replicated upload
+    would move P times the bytes over PCIe (Reddit shape: 280 MB per GPU, 5 ms).  Collective: every
+    rank of the group must call it.  Runs on the current stream."""
+    import torch.distributed as dist
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    nnz = int(col_h.numel())
+    per = max(2, ((nnz + world - 1) // world + 1) // 2 * 2)
+    lo, hi = min(nnz, rank * per), min(nnz, (rank + 1) * per)
+    rp = rp_h.to(dev, non_blocking=True)
+    out = []
+    for host, dtype in ((col_h, torch.int32), (val_h, torch.float64)):
+        piece = torch.zeros(per, dtype=dtype, device=dev)
+        if hi > lo:
+            piece[:hi - lo].copy_(host[lo:hi], non_blocking=True)
+        full = torch.empty(per * world, dtype=dtype, device=dev)
+        dist.all_gather_into_tensor(full, piece, group=group)
+        out.append(full[:nnz])
+    return rp, out[0], out[1]
+
+
 def precompute_host(adj, features, degree, standardize=False, out=None, out_blocks=None, chunk=None,
-                    col_slab=None, trace=None):
+                    col_slab=None, trace=None, group=None):
     """`sgc_precompute(features, aug_normalized_adjacency(adj), degree)` for HOST inputs, result
     in host memory.
 
@@ -124,6 +147,9 @@ def precompute_host(adj, features, degree, standardize=False, out=None, out_bloc
     standardize   apply utils.py:119 ((x - mean) / std per column, unbiased std) before the hops
     out       optional pinned fp32 [N, F] host tensor receiving the result
     out_blocks / col_slab   schedule knobs (defaults: SGC_B200_OUT_BLOCKS, default_col_slab)
+    group     torch.distributed process group whose ranks all hold the same `adj` in host memory and each
+              call with their own column block of the features (feature-sharded propagation): the
+              adjacency is then uploaded once per node -- 1/P per rank -- and all-gathered over NVLink
     trace     optional list; receives (label, milliseconds since the call started) for the device-side
               milestones of the schedule (CUDA events), for tools/e2e_sweep.py
     Returns `out` (complete when the call returns)."""
@@ -172,9 +198,12 @@ def precompute_host(adj, features, degree, standardize=False, out=None, out_bloc
         slabs = [(c0, c0 + w) for c0, w in zip(starts, widths)]
         by_cols = len(slabs) > 1
         with torch.cuda.stream(c_in):
-            rp = rp_h.to(dev, non_blocking=True)
-            col = col_h.to(dev, non_blocking=True)
-            val = val_h.to(dev, non_blocking=True)
+            if group is not None:
+                rp, col, val = _upload_csr_shared(rp_h, col_h, val_h, dev, group)
+            else:
+                rp = rp_h.to(dev, non_blocking=True)
+                col = col_h.to(dev, non_blocking=True)
+                val = val_h.to(dev, non_blocking=True)
             csr_up = torch.cuda.Event()
             csr_up.record(c_in)
             mark("csr up", c_in)

@@ -154,3 +154,40 @@ def test_feature_sharded_columns_bit_identical():
     for c0, c1 in partition_features(x.shape[1], 8):
         got = propagate_feature_sharded(g, sgc_b200.to_padded(x[:, c0:c1]), 2)
         assert torch.equal(got, want[:, c0:c1])
+
+
+def host_worker(rank, world, port, ret):
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    try:
+        import sgc_b200
+        from sgc_b200 import synth
+        from sgc_b200.dist import partition_features
+        s = synth.make_shape("reddit", device=dev, scale=0.01, seed=13)
+        n, k = s["n"], 2
+        x = s["x"][:, :200].contiguous()
+        c0, c1 = partition_features(200, world)[rank]
+        host = (n, s["row_ptr"].cpu().pin_memory(), s["col"].cpu().pin_memory(), s["val"].cpu().pin_memory())
+        xh = x[:, c0:c1].contiguous().cpu().pin_memory()
+        got = sgc_b200.precompute_host(host, xh, k, standardize=True, group=dist.group.WORLD, col_slab=64)
+        alone = sgc_b200.precompute_host(host, xh, k, standardize=True, col_slab=64)
+        graph = sgc_b200.normalize_csr(n, s["row_ptr"], s["col"], s["val"])
+        mean, std = sgc_b200.col_stats(x)
+        want, _ = sgc_b200.sgc_precompute(sgc_b200.to_padded((x - mean) / std), graph, k)
+        ret[rank] = (bool(torch.equal(got, alone)), bool(torch.equal(got, want[:, c0:c1].cpu())))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [1, 2])
+def test_host_pipeline_shared_adjacency_upload(world):
+    """precompute_host(group=...): every rank uploads 1/P of the adjacency and an NCCL all-gather
+    replicates it; the result equals the rank-local upload and the single-GPU columns bit for bit."""
+    if torch.cuda.device_count() < world:
+        pytest.skip("needs %d GPUs" % world)
+    ret = mp.Manager().dict()
+    mp.spawn(host_worker, args=(world, free_port(), ret), nprocs=world, join=True)
+    for rank in range(world):
+        assert ret[rank] == (True, True), (rank, ret[rank])
