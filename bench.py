@@ -225,7 +225,12 @@ def run_own(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # NCCL's banner / logs off stdout: ONE JSON line
+        # NCCL prints its version banner to fd 1 from C; keep stdout for the ONE JSON line: everything
+        # written to fd 1 from here on goes to stderr, the JSON line is written to the saved descriptor
+        sys.stdout.flush()
+        saved = os.dup(1)
+        os.dup2(2, 1)
+        sys.stdout = os.fdopen(saved, "w")
         dist.init_process_group("nccl", device_id=dev)
     if world > 1:
         from sgc_b200 import dist as sgc_dist

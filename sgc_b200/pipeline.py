@@ -30,6 +30,7 @@ values, split plans) runs while the features are still crossing PCIe.
     block b is copied back while block b+1 is computed.
 """
 import os
+import time
 
 import torch
 
@@ -85,7 +86,11 @@ def default_col_slab(n, f):
         return w if 0 < w < f else 0
     for w in (256, 128, 64, 32):
         if n * w * 4 <= L2_SLAB_BUDGET:
-            return w if w < f else 0
+            # at least two full slabs: with fewer the pipeline has nothing to overlap, and strided H2D
+            # copies whose host pitch is only slightly larger than the slab (512-byte pieces at a
+            # 520..600-byte pitch) run at 5-13 GB/s instead of 35-46 (tools/copy2d_probe.py,
+            # profiles/r01_copy2d_probe.log) -- such blocks take the contiguous row-block schedule
+            return w if 2 * w <= f else 0
     return 0
 
 
@@ -150,9 +155,10 @@ def precompute_host(adj, features, degree, standardize=False, out=None, out_bloc
     group     torch.distributed process group whose ranks all hold the same `adj` in host memory and each
               call with their own column block of the features (feature-sharded propagation): the
               adjacency is then uploaded once per node -- 1/P per rank -- and all-gathered over NVLink
-    trace     optional list; receives (label, milliseconds since the call started) for the device-side
-              milestones of the schedule (CUDA events), for tools/e2e_sweep.py
+    trace     optional list; receives (label, device ms since the start mark, host ms since the call) for
+              the milestones of the schedule (CUDA events), for tools/e2e_sweep.py
     Returns `out` (complete when the call returns)."""
+    t_call = time.perf_counter()
     dev = require_cuda()
     degree = int(degree)
     if degree < 1:
@@ -187,7 +193,7 @@ def precompute_host(adj, features, degree, standardize=False, out=None, out_bloc
             if trace is not None:
                 e = torch.cuda.Event(enable_timing=True)
                 e.record(stream)
-                marks.append((label, e))
+                marks.append((label, e, (time.perf_counter() - t_call) * 1e3))
 
         x = padded_rows(n, f, dev)
         ld = x.stride(0)
@@ -277,5 +283,7 @@ def precompute_host(adj, features, degree, standardize=False, out=None, out_bloc
         c_out.synchronize()
         if trace is not None:
             main.synchronize()
-            trace.extend((label, marks[0][1].elapsed_time(e)) for label, e in marks)
+            # (label, device ms since the start mark, host ms since the call when the mark was enqueued)
+            trace.extend((label, marks[0][1].elapsed_time(e), h) for label, e, h in marks)
+            trace.append(("returned", marks[0][1].elapsed_time(marks[-1][1]), (time.perf_counter() - t_call) * 1e3))
     return out

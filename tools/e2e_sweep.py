@@ -69,8 +69,8 @@ for ws in ([128] * 4 + [90], [128] * 4 + [64, 26], [64] + [128] * 4 + [26]):
 tr = []
 sgc_b200.precompute_host(csr, host["x"], k, standardize=True, out=out, trace=tr)
 print("device-side timeline of the default schedule (ms since start):")
-for label, ms in tr:
-    print("   %8.2f  %s" % (ms, label))
+for label, ms, host_ms in tr:
+    print("   %8.2f  (enqueued at %6.2f)  %s" % (ms, host_ms, label))
 
 
 def copy2d_only():
