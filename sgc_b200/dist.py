@@ -419,9 +419,9 @@ def propagate_feature_sharded(graph, x_cols, degree, **kw):
 def run_feature_sharded_workload(name, args, rank, world, dev, B, with_e2e=True, want_single=True):
     """bench leg for sharding == 'features' (see run_sharded_workload for the contract)."""
     from . import _ffi, synth
-    from .features import StandardizedFeatures, col_stats, standardize_, to_padded
+    from .features import col_stats, standardize_, to_padded
     from .graph import normalize_csr
-    from .propagate import default_chunk, propagate, sgc_precompute
+    from .propagate import default_chunk, propagate
     shape = synth.SHAPES[name]
     n, f, k = shape["n"], shape["f"], shape["k"]
     c0, c1 = partition_features(f, world)[rank]

@@ -193,3 +193,37 @@ def test_standardized_features_semantics():
     assert feats.cuda is not None and feats.float() is feats
     rawt, m, s = feats.unwrap()
     assert type(rawt) is torch.Tensor and rawt.data_ptr() == raw.data_ptr() and m is mean and s is std
+
+
+def test_host_pipeline_schedule_choice(monkeypatch):
+    """pipeline.default_col_slab / slab_widths: column slabs only when a slab fits L2 and the block holds
+    at least two full slabs (otherwise the contiguous row-block schedule); no CPU path."""
+    import torch
+    from sgc_b200 import _ffi, pipeline
+    monkeypatch.delenv("SGC_B200_COL_SLAB", raising=False)
+    n_reddit, n_products = 232965, 2449029
+    assert pipeline.default_col_slab(n_reddit, 602) == 128
+    assert pipeline.slab_widths(602, 128) == [128, 128, 128, 128, 90]
+    assert pipeline.default_col_slab(n_reddit, 301) == 128 and pipeline.slab_widths(301, 128) == [128, 128, 45]
+    for f in (80, 138, 160, 255):                  # column blocks of the 4- and 8-GPU feature sharding
+        assert pipeline.default_col_slab(n_reddit, f) == 0 and pipeline.slab_widths(f, 0) == [f]
+    assert pipeline.default_col_slab(n_products, 100) == 0          # one slab (and none fits L2)
+    assert pipeline.default_col_slab(2708, 1433) == 256             # Cora: everything fits, widest slab
+    monkeypatch.setenv("SGC_B200_COL_SLAB", "64")
+    assert pipeline.default_col_slab(n_reddit, 602) == 64 and pipeline.default_col_slab(n_reddit, 60) == 0
+    if not torch.cuda.is_available():
+        with pytest.raises(_ffi.SgcError):
+            pipeline.precompute_host((2, torch.tensor([0, 1, 2]), torch.tensor([1, 0], dtype=torch.int32),
+                                      torch.ones(2, dtype=torch.float64)), torch.ones(2, 3), 1)
+
+
+def test_textsgc_and_sparse_feature_entry_points_have_no_cpu_path():
+    import scipy.sparse as sp
+    import torch
+    from sgc_b200 import _ffi, sparse_features, textsgc
+    if torch.cuda.is_available():
+        pytest.skip("CPU-only check")
+    a = sp.identity(4, format="csr", dtype=np.float32)
+    for fn in (textsgc.preprocess_adj, textsgc.normalize_adj, sparse_features.row_normalize):
+        with pytest.raises(_ffi.SgcError):
+            fn(a)

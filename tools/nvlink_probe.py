@@ -2,7 +2,7 @@
   1. sgc_push_rows: pure remote stores of [rows, f] pieces to every peer (GB/s egress per GPU)
   2. the sharded hop on this rank's rows: no push / push to peers
     python -m torch.distributed.run --nproc-per-node 2 tools/nvlink_probe.py [workload] [scale]"""
-import os, sys, time
+import os, sys
 import numpy as np
 import torch
 import torch.distributed as dist

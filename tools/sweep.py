@@ -1,6 +1,6 @@
 """Parameter sweep of the hop kernel on the Reddit-shaped (or other) workload; prints ms per hop.
 Run on the GPU box:  python tools/sweep.py [workload]"""
-import itertools, json, os, sys
+import os, sys
 import numpy as np
 import torch
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
