@@ -116,3 +116,68 @@ def test_sparse_hop_wide_and_long_rows(dev):
     wide = SparseFeatures.from_scipy(sp.csr_matrix((n, 60000), dtype=np.float32), dev)
     with pytest.raises(_ffi.SgcError):
         hop_sparse_x(graph, wide)
+
+
+def test_load_citation_on_synthetic_planetoid_files(dev, tmp_path, monkeypatch):
+    """utils.load_citation end to end on files in the Planetoid layout the reference reads
+    (utils.py:32-90): adjacency normalised on the GPU, features row-normalised and densified on the GPU
+    (fp32 CSR in, as in Cora), labels / splits as the reference builds them, and sgc_precompute on the
+    returned tensors (sparse first hop) equal to the oracle."""
+    import os
+    import pickle
+    import sgc_b200
+    from sgc_b200 import utils as U
+    from sgc_b200.sparse_features import sparse_origin
+    from oracle import normalization_oracle as no, spmm_oracle as so
+    rng = np.random.RandomState(8)
+    n_train, n_all, n_test, f, c = 40, 700, 120, 300, 4
+    n = n_all + n_test
+    feats = sp.random(n, f, density=0.03, random_state=rng, format="csr", dtype=np.float32)
+    feats.data[:] = 1.0                                            # bag-of-words, like Cora
+    lab = rng.randint(0, c, n)
+    onehot = np.eye(c, dtype=np.int32)[lab]
+    test_order = n_all + rng.permutation(n_test)                   # ind.<ds>.test.index is unsorted
+    test_sorted = np.sort(test_order)
+    src, dst = rng.randint(0, n, 2500), rng.randint(0, n, 2500)
+    graph = {i: [] for i in range(n)}
+    for a, b in zip(src.tolist(), dst.tolist()):
+        graph[a].append(b)
+        graph[b].append(a)
+    os.makedirs(tmp_path / "data")
+    # rows n_all.. of the stored matrices are in test.index order (the loader undoes that, utils.py:60-61)
+    stored = feats.tolil()
+    stored[test_sorted, :] = feats[test_order, :]
+    stored = stored.tocsr()
+    lab_stored = onehot.copy()
+    lab_stored[test_sorted] = onehot[test_order]
+    parts = {"x": stored[:n_train], "y": lab_stored[:n_train], "tx": stored[n_all:], "ty": lab_stored[n_all:],
+             "allx": stored[:n_all], "ally": lab_stored[:n_all], "graph": graph}
+    for key, obj in parts.items():
+        with open(tmp_path / "data" / ("ind.synth.%s" % key), "wb") as fh:
+            pickle.dump(obj, fh)
+    with open(tmp_path / "data" / "ind.synth.test.index", "w") as fh:
+        fh.write("\n".join(str(int(i)) for i in test_order) + "\n")
+    monkeypatch.chdir(tmp_path)
+    adj, features, labels, idx_train, idx_val, idx_test = U.load_citation("synth", "AugNormAdj", True)
+    # expected adjacency: symmetric binary graph of the dict (self-loops stay), then normalisation
+    a = sp.coo_matrix((np.ones(2 * src.size), (np.r_[src, dst], np.r_[dst, src])), shape=(n, n)).tocsr()
+    a.data[:] = 1.0
+    a.sort_indices()
+    ref = no.aug_normalized_adjacency_oracle(n, a.indptr, a.indices, a.data)
+    assert np.array_equal(adj.row_ptr.cpu().numpy(), ref["indptr"])
+    assert np.array_equal(adj.col.cpu().numpy().astype(np.int64), ref["indices"])
+    assert np.array_equal(adj.values32().cpu().numpy(), ref["data"].astype(np.float32))
+    # expected features: the loader's reordering puts node i's features in row i; then row_normalize
+    fc = feats.tocsr()
+    fc.sort_indices()
+    ptr, idx, val = no.row_normalize_oracle(n, fc.indptr, fc.indices, fc.data)
+    want_x = np.zeros((n, f), dtype=np.float32)
+    want_x[np.repeat(np.arange(n), np.diff(ptr)), idx] = val
+    assert features.is_cuda and features.dtype == torch.float32 and np.array_equal(features.cpu().numpy(), want_x)
+    assert sparse_origin(features) is not None
+    assert np.array_equal(labels.cpu().numpy(), lab)
+    assert idx_train.tolist() == list(range(n_train)) and idx_val.tolist() == list(range(n_train, n_train + 500))
+    assert idx_test.tolist() == test_sorted.tolist()
+    y, _ = sgc_b200.sgc_precompute(features, adj, 2)              # citation.py:32
+    want, _ = so.sgc_precompute_oracle(want_x, ref["indptr"], ref["indices"], ref["data"].astype(np.float32), 2)
+    assert np.array_equal(y.cpu().numpy(), want)
