@@ -49,7 +49,7 @@ def default_std_mode():
 def fused_norm():
     """SGC_B200_FUSED_NORM=1: the hop forms fp32((d_i*a_ij)*d_j) on the fly from the fp64 values of
     A+I and D^-1/2, so S is never materialised (8 B + a D^-1/2 gather per stored entry and slab
-    pass).  Default 0: the same fp32 values are written once by sgc_norm_build (4 B per entry,
+    pass).  Default 0: the same fp32 values are written once by sgc_norm_values at normalisation time (4 B per entry,
     cached on the graph) and streamed by every hop -- bit-identical results, and measured 8-13 %
     faster per hop on the Reddit shape (4.65 ms vs 5.1-5.4 ms), see DESIGN.md."""
     return _ENV("SGC_B200_FUSED_NORM", "0") == "1"
