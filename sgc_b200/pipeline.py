@@ -236,7 +236,11 @@ def precompute_host(adj, features, degree, standardize=False, out=None, out_bloc
             graph.plan(chunk)
             blocks = None
         else:
-            blocks = row_blocks(graph, default_out_blocks() if out_blocks is None else int(out_blocks))
+            # row blocks pay when the gathered operand is L2-resident (Reddit-sized column blocks: 35 ->
+            # 31 ms); when X is far larger than L2 every block launch re-streams it and re-tags the hub
+            # columns (products shape: 89 ms with one launch, 96 ms with eight) -> one launch
+            big = n * 32 * 4 > L2_SLAB_BUDGET
+            blocks = row_blocks(graph, (1 if big else default_out_blocks()) if out_blocks is None else int(out_blocks))
             if degree > 1:
                 graph.plan(chunk)
             for _, _, sub in blocks:
