@@ -65,6 +65,14 @@ int32_t sgc_l2_set_persisting_bytes(int64_t bytes, int64_t *granted_out);
  * still crossing PCIe.  Host memory must be pinned for the copy to be asynchronous. */
 int32_t sgc_copy_2d(void *dst, int64_t dst_pitch_bytes, const void *src, int64_t src_pitch_bytes,
                     int64_t width_bytes, int64_t rows, void *stream);
+/* Host-side: 1 if every one of the n doubles at v_host is bit-equal to `value`, 0 if not, 2 if the
+ * scan gave up after budget_us microseconds (<= 0: no budget), -1 on bad arguments; `threads`
+ * workers, memory-bound, early exit.  The stored values of the reference's adjacency matrices are
+ * constant (1.0: utils.py:62 networkx adjacency; 2.0: utils.py:116 adj + adj.T of the symmetric 0/1
+ * Reddit matrix); the host pipeline then fills the device value array instead of uploading nnz x 8
+ * bytes.  No GPU work. */
+int32_t sgc_host_all_equal_f64(const double *v_host, int64_t n, double value, int32_t threads,
+                               int64_t budget_us);
 
 /* ---- generic device primitives ------------------------------------------------------------ */
 size_t  sgc_scan_workspace_bytes(int64_t n);

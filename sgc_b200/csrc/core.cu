@@ -1,9 +1,12 @@
 // Housekeeping entry points and the device-wide exclusive scan used by every compaction step
 // (self-loop insertion, zero-product pruning, long-row split table, transpose, sub-graph).
 #include <atomic>
+#include <chrono>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <thread>
+#include <vector>
 
 #include "common.cuh"
 
@@ -195,6 +198,55 @@ int32_t sgc_copy_2d(void *dst, int64_t dst_pitch_bytes, const void *src, int64_t
                                    (size_t)width_bytes, (size_t)rows, cudaMemcpyDefault,
                                    sgc::as_stream(stream)));
     return SGC_OK;
+}
+
+
+// Host-side helper of the host-to-host pipeline (pipeline.py): is every one of the n doubles at v (host
+// memory) bit-equal to `value`?  Adjacency matrices of the reference's loaders are constant-valued (1.0:
+// utils.py:62 networkx adjacency; 2.0: utils.py:116, adj + adj.T of the symmetric 0/1 Reddit matrix); the
+// pipeline then fills the device array instead of sending nnz x 8 bytes over PCIe.  Memory-bound: `threads` workers
+// over contiguous pieces, early exit once any piece has seen a mismatch or the time budget is spent
+// (budget_us <= 0: none) -- the scan only pays while it is cheaper than the upload it saves.
+// Returns 1 all equal / 0 not / 2 gave up on the budget / -1 bad input.
+int32_t sgc_host_all_equal_f64(const double *v, int64_t n, double value, int32_t threads, int64_t budget_us)
+{
+    if (n < 0 || (n > 0 && v == nullptr)) return -1;
+    if (n == 0) return 1;
+    uint64_t want;
+    memcpy(&want, &value, sizeof(want));
+    const uint64_t *w = reinterpret_cast<const uint64_t *>(v);
+    using clock = std::chrono::steady_clock;
+    const clock::time_point deadline = clock::now() + std::chrono::microseconds(budget_us > 0 ? budget_us : 0);
+    std::atomic<int> state{1};                         // 1 equal so far, 0 differs, 2 out of time
+    auto scan = [&](int64_t lo, int64_t hi) {
+        constexpr int64_t STEP = 1 << 15;              // 256 KB between looks at the flag and the clock
+        for (int64_t b = lo; b < hi; b += STEP) {
+            if (state.load(std::memory_order_relaxed) != 1) return;
+            if (budget_us > 0 && clock::now() > deadline) {
+                int expect = 1;
+                state.compare_exchange_strong(expect, 2, std::memory_order_relaxed);
+                return;
+            }
+            const int64_t e = b + STEP < hi ? b + STEP : hi;
+            uint64_t acc = 0;
+            for (int64_t i = b; i < e; ++i) acc |= w[i] ^ want;
+            if (acc) { state.store(0, std::memory_order_relaxed); return; }
+        }
+    };
+    int64_t t = threads < 1 ? 1 : threads;
+    if (t > 64) t = 64;
+    if (n < t * (int64_t)(1 << 16)) t = 1 + (n >> 16);  // at least 512 KB per worker
+    if (t <= 1) { scan(0, n); return state.load(); }
+    const int64_t per = (n + t - 1) / t;
+    std::vector<std::thread> pool;
+    pool.reserve((size_t)t - 1);
+    for (int64_t k = 1; k < t; ++k) {
+        const int64_t lo = k * per, hi = lo + per < n ? lo + per : n;
+        if (lo < hi) pool.emplace_back(scan, lo, hi);
+    }
+    scan(0, per < n ? per : n);
+    for (auto &th : pool) th.join();
+    return state.load();
 }
 
 }  // extern "C"

@@ -495,7 +495,7 @@ def run_feature_sharded_workload(name, args, rank, world, dev, B, with_e2e=True,
             # this rank's column block through the pipelined host-to-host path (pipeline.py): CSR up,
             # K1/K2 under the upload of X, per slab K3 + hops + strided D2H
             precompute_host(host_csr, host["x"], k, standardize=bool(shape["scaled"]), out=out_host,
-                            group=dist.group.WORLD if shared_csr else None)
+                            group=dist.group.WORLD if shared_csr else None, detect_uniform_values=False)
 
         e2e_step()
         dist.barrier()

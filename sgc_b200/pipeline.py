@@ -140,8 +140,44 @@ def _upload_csr_shared(rp_h, col_h, val_h, dev, group):
     return rp, out[0], out[1]
 
 
+def host_threads():
+    """Workers of the host-side scan of the adjacency values (SGC_B200_HOST_THREADS)."""
+    return max(1, int(os.environ.get("SGC_B200_HOST_THREADS", min(8, os.cpu_count() or 1))))
+
+
+PCIE_BYTES_PER_US = 40e3        # ~40 GB/s: sustained pinned H2D rate of the strided / contiguous copies
+_scan_gave_up = False           # this host scans slower than PCIe uploads: stop trying (per process)
+
+
+def uniform_value(val_h, hidden_bytes=0):
+    """The common value when every stored value of the host CSR holds the same bits, else None.  The
+    reference's adjacency matrices are constant-valued: 1.0 for the networkx adjacency of the citation
+    graphs (utils.py:62), 2.0 for Reddit (`adj + adj.T` of a symmetric 0/1 matrix, utils.py:116); the
+    device array is then filled in place of an nnz x 8-byte upload.  Exact -- a threaded bit compare over
+    the whole array (sgc_host_all_equal_f64), run while the DMA engine is busy with the `hidden_bytes`
+    enqueued ahead of it.  The scan gets the time those copies take plus the time the upload it replaces
+    would take; a host that cannot finish within that (it would lose time, not save it) gives up,
+    uploads, and does not try again in this process.  SGC_B200_UNIFORM_VALUES=0 switches the scan off,
+    =force removes the time budget."""
+    global _scan_gave_up
+    mode = os.environ.get("SGC_B200_UNIFORM_VALUES", "1")
+    if mode == "0" or (_scan_gave_up and mode != "force"):
+        return None
+    if val_h.dtype != torch.float64 or not val_h.is_contiguous() or val_h.is_cuda or val_h.numel() == 0:
+        return None
+    first = float(val_h[0])
+    if first != first or first in (float("inf"), float("-inf")):       # NaN payloads would not survive the fill
+        return None
+    nbytes = int(val_h.numel()) * 8
+    budget_us = 0 if mode == "force" else max(500, int((hidden_bytes + nbytes) / PCIE_BYTES_PER_US))
+    r = _ffi.lib().sgc_host_all_equal_f64(val_h.data_ptr(), int(val_h.numel()), first, host_threads(), budget_us)
+    if r == 2:
+        _scan_gave_up = True
+    return first if r == 1 else None
+
+
 def precompute_host(adj, features, degree, standardize=False, out=None, out_blocks=None, chunk=None,
-                    col_slab=None, trace=None, group=None):
+                    col_slab=None, trace=None, group=None, detect_uniform_values=None, stats=None):
     """`sgc_precompute(features, aug_normalized_adjacency(adj), degree)` for HOST inputs, result
     in host memory.
 
@@ -155,6 +191,10 @@ def precompute_host(adj, features, degree, standardize=False, out=None, out_bloc
     group     torch.distributed process group whose ranks all hold the same `adj` in host memory and each
               call with their own column block of the features (feature-sharded propagation): the
               adjacency is then uploaded once per node -- 1/P per rank -- and all-gathered over NVLink
+    detect_uniform_values   scan the stored values on the host and, when they are all the same, fill the
+              device array instead of uploading it (`uniform_value`); default: on unless `group` is given
+    stats     optional dict; receives h2d_bytes / d2h_bytes actually copied by this call and
+              uniform_value (the fill value, or None when the values were uploaded)
     trace     optional list; receives (label, device ms since the start mark, host ms since the call) for
               the milestones of the schedule (CUDA events), for tools/e2e_sweep.py
     Returns `out` (complete when the call returns)."""
@@ -204,17 +244,9 @@ def precompute_host(adj, features, degree, standardize=False, out=None, out_bloc
         slabs = [(c0, c0 + w) for c0, w in zip(starts, widths)]
         by_cols = len(slabs) > 1
         with torch.cuda.stream(c_in):
-            if group is not None:
-                rp, col, val = _upload_csr_shared(rp_h, col_h, val_h, dev, group)
-            else:
-                rp = rp_h.to(dev, non_blocking=True)
-                col = col_h.to(dev, non_blocking=True)
-                val = val_h.to(dev, non_blocking=True)
-            csr_up = torch.cuda.Event()
-            csr_up.record(c_in)
-            mark("csr up", c_in)
             x_up = []
-            for c0, c1 in slabs:
+
+            def upload_slab(c0, c1):
                 if by_cols:
                     _ffi.call("sgc_copy_2d", x.data_ptr() + 4 * c0, 4 * ld, features.data_ptr() + 4 * c0, 4 * f,
                               4 * (c1 - c0), n, c_in.cuda_stream)
@@ -224,6 +256,36 @@ def precompute_host(adj, features, degree, standardize=False, out=None, out_bloc
                 e.record(c_in)
                 x_up.append(e)
                 mark("x[:, %d:%d] up" % (c0, c1), c_in)
+
+            nbytes = lambda t: t.numel() * t.element_size()
+            h2d = nbytes(rp_h) + nbytes(features)
+            fill = None
+            if group is not None:
+                rp, col, val = _upload_csr_shared(rp_h, col_h, val_h, dev, group)
+                h2d += -(-(nbytes(col_h) + nbytes(val_h)) // torch.distributed.get_world_size(group))
+            else:
+                rp = rp_h.to(dev, non_blocking=True)
+                col = col_h.to(dev, non_blocking=True)
+                h2d += nbytes(col_h)
+                if detect_uniform_values or detect_uniform_values is None:
+                    ahead = nbytes(col_h)
+                    if by_cols:
+                        upload_slab(*slabs[0])                 # keeps the DMA engine fed during the host scan
+                        ahead += n * 4 * (slabs[0][1] - slabs[0][0])
+                    fill = uniform_value(val_h, ahead)
+                    mark("values scanned", c_in)
+                if fill is not None:
+                    val = torch.full((val_h.numel(),), fill, dtype=torch.float64, device=dev)
+                else:
+                    val = val_h.to(dev, non_blocking=True)
+                    h2d += nbytes(val_h)
+            csr_up = torch.cuda.Event()
+            csr_up.record(c_in)
+            mark("csr up", c_in)
+            for c0, c1 in slabs[len(x_up):]:
+                upload_slab(c0, c1)
+            if stats is not None:
+                stats.update(h2d_bytes=int(h2d), d2h_bytes=int(n * f * 4), uniform_value=fill)
         for t in (rp, col, val):
             t.record_stream(main)
         x.record_stream(c_in)

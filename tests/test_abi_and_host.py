@@ -217,6 +217,49 @@ def test_host_pipeline_schedule_choice(monkeypatch):
                                       torch.ones(2, dtype=torch.float64)), torch.ones(2, 3), 1)
 
 
+def test_host_value_scan(built, monkeypatch):
+    """sgc_host_all_equal_f64 (host-side, no GPU work) and pipeline.uniform_value: exact bit compare,
+    threaded, position-independent; non-fp64 / strided / weighted arrays are never taken for constant."""
+    from sgc_b200 import pipeline
+    fn = built.lib().sgc_host_all_equal_f64
+    rng = np.random.default_rng(3)
+    for n in (0, 1, 5, 65535, 65536, 65537, 1 << 20, (1 << 20) + 3):
+        v = np.ones(n, dtype=np.float64)
+        for threads in (1, 3, 8, 200):
+            assert fn(v.ctypes.data, n, 1.0, threads, 0) == 1
+        for pos in ([0, n - 1, n // 2] + list(rng.integers(0, n, 3)) if n else []):
+            for bad in (0.0, 2.0, -1.0, np.nan, np.nextafter(1.0, 2.0)):
+                w = v.copy()
+                w[pos] = bad
+                assert fn(w.ctypes.data, n, 1.0, 4, 0) == 0, (n, pos, bad)
+    z = np.array([0.0, -0.0], dtype=np.float64)
+    assert fn(z.ctypes.data, 2, 0.0, 1, 0) == 0             # bit compare: -0.0 is not 0.0
+    assert fn(None, 3, 1.0, 1, 0) == -1 and fn(None, 0, 1.0, 1, 0) == 1
+    big = np.ones(1 << 22, dtype=np.float64)
+    assert fn(big.ctypes.data, big.size, 1.0, 1, 1) in (1, 2)      # 1 us budget: may give up, never lies
+    big[-1] = 7.0
+    assert fn(big.ctypes.data, big.size, 1.0, 1, 1) in (0, 2)
+
+    monkeypatch.setenv("SGC_B200_UNIFORM_VALUES", "force")
+    twos = torch.full((100000,), 2.0, dtype=torch.float64)
+    assert pipeline.uniform_value(twos) == 2.0 and pipeline.uniform_value(twos[:1]) == 2.0
+    assert pipeline.uniform_value(torch.ones(70000, dtype=torch.float64)) == 1.0
+    assert pipeline.uniform_value(twos[:0]) is None                      # nothing to save
+    assert pipeline.uniform_value(twos.float()) is None and pipeline.uniform_value(twos[::2]) is None
+    assert pipeline.uniform_value(torch.full((10,), float("nan"), dtype=torch.float64)) is None
+    twos[77777] = 3.0
+    assert pipeline.uniform_value(twos) is None
+    twos[77777] = 2.0
+    monkeypatch.setenv("SGC_B200_UNIFORM_VALUES", "0")
+    assert pipeline.uniform_value(twos) is None
+    # a host that cannot finish inside the budget gives up once and stops scanning in this process
+    monkeypatch.setenv("SGC_B200_UNIFORM_VALUES", "1")
+    monkeypatch.setattr(pipeline, "_scan_gave_up", True)
+    assert pipeline.uniform_value(twos) is None
+    monkeypatch.setattr(pipeline, "_scan_gave_up", False)
+    assert pipeline.uniform_value(twos, hidden_bytes=1 << 30) == 2.0
+
+
 def test_textsgc_and_sparse_feature_entry_points_have_no_cpu_path():
     import scipy.sparse as sp
     import torch

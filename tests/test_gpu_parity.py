@@ -339,6 +339,57 @@ def test_precompute_host_pipeline(dev, blocks, col_slab):
     assert np.array_equal(got3.numpy(), want2)
 
 
+@pytest.mark.parametrize("col_slab", [None, 32])
+def test_precompute_host_uniform_values(dev, monkeypatch, col_slab):
+    """A constant-valued adjacency (what the reference's loaders hold: 1.0 for the citation graphs,
+    2.0 for Reddit's adj + adj.T) is recognised on the host and its value array filled on the GPU
+    instead of uploaded: same bits as the uploading path, nnz x 8 fewer bytes over PCIe; a weighted
+    adjacency is uploaded as is and matches the device-resident path."""
+    import sgc_b200
+    s, graph = powerlaw_case(dev, scale=0.01, seed=11)
+    n = s["n"]
+    common = float(s["val"][0])
+    assert bool((s["val"] == common).all())
+    x = s["x"][:, :77].contiguous()
+    x_host = x.cpu().pin_memory()
+    host = (n, s["row_ptr"].cpu().pin_memory(), s["col"].cpu().pin_memory(), s["val"].cpu().pin_memory())
+    want, _ = sgc_b200.sgc_precompute(sgc_b200.to_padded(x.clone()), graph, 2)
+    runs = {}
+    for mode in ("force", "0"):
+        monkeypatch.setenv("SGC_B200_UNIFORM_VALUES", mode)
+        st = {}
+        got = sgc_b200.precompute_host(host, x_host, 2, col_slab=col_slab, stats=st)
+        assert torch.equal(got, want.cpu())
+        runs[mode] = st
+    assert runs["force"]["uniform_value"] == common and runs["0"]["uniform_value"] is None
+    assert runs["0"]["h2d_bytes"] - runs["force"]["h2d_bytes"] == host[3].numel() * 8
+    assert runs["0"]["h2d_bytes"] == sum(t.numel() * t.element_size() for t in host[1:]) + x_host.numel() * 4
+    assert runs["0"]["d2h_bytes"] == n * 77 * 4
+    # explicit switch wins over the environment
+    monkeypatch.setenv("SGC_B200_UNIFORM_VALUES", "force")
+    st = {}
+    sgc_b200.precompute_host(host, x_host, 1, col_slab=col_slab, stats=st, detect_uniform_values=False)
+    assert st["uniform_value"] is None
+    # the other constant of the reference's loaders
+    ones = torch.ones_like(s["val"])
+    g1 = sgc_b200.normalize_csr(n, s["row_ptr"], s["col"], ones)
+    want1, _ = sgc_b200.sgc_precompute(sgc_b200.to_padded(x.clone()), g1, 2)
+    st = {}
+    got1 = sgc_b200.precompute_host((n, host[1], host[2], ones.cpu().pin_memory()), x_host, 2, col_slab=col_slab,
+                                    stats=st)
+    assert st["uniform_value"] == 1.0 and torch.equal(got1, want1.cpu())
+    # weighted adjacency: one stored value differs (the last one: the scan has to reach it)
+    val2 = s["val"].clone()
+    val2[-1] = 2.5
+    g2 = sgc_b200.normalize_csr(n, s["row_ptr"], s["col"], val2)
+    want2, _ = sgc_b200.sgc_precompute(sgc_b200.to_padded(x.clone()), g2, 2)
+    st = {}
+    got2 = sgc_b200.precompute_host((n, host[1], host[2], val2.cpu().pin_memory()), x_host, 2, col_slab=col_slab,
+                                    stats=st)
+    assert st["uniform_value"] is None and torch.equal(got2, want2.cpu())
+    assert not torch.equal(got2, want.cpu())
+
+
 def test_downstream_accuracy_unchanged(dev):
     """Cora / Citeseer: the reference's own training loop (citation.py:35-62, restated here as test
     code, CPU, seed 42, tuned weight decay) on the GPU-propagated features gives the reference's
