@@ -309,6 +309,13 @@ def run_own(args):
             hop_ms["fused_std_" + mode] = hop_time(
                 lambda: sgc_b200.hop(graph, x_raw, mean=mean32, std=std32, std_mode=mode, out=ybuf))
     del x_raw
+    incumbent = None
+    if not args.skip_incumbent:
+        try:
+            incumbent = gpu_incumbent(graph, x, f, hop_time, hop_ms["plain"])
+        except Exception as exc:        # reported for context only: never costs the primary line
+            incumbent = {"error": repr(exc)[:300]}
+        torch.cuda.empty_cache()
     peak, peak_src = peaks()
     b_hop = hop_bytes(n, nnz, f)
     avg_launch_s = ms_per_step * 1e-3 / k
@@ -366,9 +373,26 @@ def run_own(args):
                                                "utils.py:93-96 times them; K1/K2/K3 + standardisation "
                                                "timed separately (above) and inside e2e"),
         "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
-        "other_workloads": others,
+        "gpu_incumbent": incumbent, "other_workloads": others,
     }
     print(json.dumps(line))
+
+
+def gpu_incumbent(graph, x, f, hop_time, ours_ms):
+    """the on-box GPU incumbent for one hop on the same S and X, as context for the
+    kernel time (library calls, outside every timed region of this bench): the reference's own CUDA path
+    -- torch.spmm on the uncoalesced fp32 COO tensor its loaders build (utils.py:23-30, 95) -- and
+    cuSPARSE on a CSR tensor of the same matrix."""
+    coo = graph.to_torch_sparse()
+    xd = x[:, :f].contiguous()
+    torch.spmm(coo, xd)
+    coo_ms = hop_time(lambda: torch.spmm(coo, xd))
+    csr = coo.coalesce().to_sparse_csr()
+    torch.mm(csr, xd)
+    csr_ms = hop_time(lambda: torch.mm(csr, xd))
+    return {"unit": "ms per hop", "torch_spmm_coo": coo_ms, "torch_mm_csr_cusparse": csr_ms,
+            "spmm_hop_kernel": ours_ms,
+            "note": "torch.spmm(COO) is what utils.py:95 runs on a GPU in the reference; library calls, reported only"}
 
 
 def single_gpu_extra(name, dev, peak):
@@ -479,6 +503,7 @@ def main():
     ap.add_argument("--workload", default=None, choices=[None, "reddit", "products", "papers100m"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--skip-e2e", action="store_true", help="profiling runs only: leaves e2e null")
+    ap.add_argument("--skip-incumbent", action="store_true", help="do not time torch.spmm / cuSPARSE beside the hop")
     args = ap.parse_args()
     args.workload_given = args.workload is not None
     if args.workload is None:

@@ -5,7 +5,7 @@ set -u
 mkdir -p gpurun_out
 timeout 900 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"
 cat gpurun_out/bench.json
-CMD="python bench.py --steps 3 --warmup 3 --no-cpu-baseline --skip-e2e --workload reddit"
+CMD="python bench.py --steps 3 --warmup 3 --no-cpu-baseline --skip-e2e --skip-incumbent --workload reddit"
 $CMD > gpurun_out/bench_short.json 2>&1; echo "short rc=$?"
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_launch.log 2>&1; echo "ncu launches rc=$?"
 python tools/profile_norm.py > gpurun_out/profile_norm.log 2>&1; echo "norm rc=$?"
