@@ -491,11 +491,13 @@ def run_feature_sharded_workload(name, args, rank, world, dev, B, with_e2e=True,
         shared_csr = os.environ.get("SGC_B200_SHARED_CSR", "1") != "0" and \
             all(b > a for a, b in partition_features(f, world))       # the all-gather needs every rank
 
+        st = {}
+
         def e2e_step():
             # this rank's column block through the pipelined host-to-host path (pipeline.py): CSR up,
             # K1/K2 under the upload of X, per slab K3 + hops + strided D2H
             precompute_host(host_csr, host["x"], k, standardize=bool(shape["scaled"]), out=out_host,
-                            group=dist.group.WORLD if shared_csr else None, detect_uniform_values=False)
+                            group=dist.group.WORLD if shared_csr else None, stats=st)
 
         e2e_step()
         dist.barrier()
@@ -506,17 +508,19 @@ def run_feature_sharded_workload(name, args, rank, world, dev, B, with_e2e=True,
         dist.barrier()
         e2e_s = torch.tensor([(time.perf_counter() - t0) / e2e_steps], dtype=torch.float64, device=dev)
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
-        mine = sum(t.numel() * t.element_size() for t in host.values())
-        if shared_csr:                                   # col / val: 1/P per rank, the rest over NVLink
-            mine -= (host["col"].numel() * 4 + host["val"].numel() * 8) * (world - 1) // world
-        h2d = torch.tensor([mine], dtype=torch.int64, device=dev)
+        # bytes this rank actually copied (col / val: 1/P per rank when shared, the rest over NVLink; a
+        # constant value array is filled on the GPU, not uploaded), summed over ranks
+        h2d = torch.tensor([st["h2d_bytes"]], dtype=torch.int64, device=dev)
         dist.all_reduce(h2d)
         out["e2e"] = {"value": k * nnz * f / float(e2e_s.item()), "unit": B["UNIT"],
                       "h2d_bytes_per_step": int(h2d.item()), "d2h_bytes_per_step": int(n * f * 4),
                       "ms_per_step": float(e2e_s.item()) * 1e3,
                       "path": "per rank: sgc_b200.precompute_host on its column block (pipeline.py); adjacency "
                               + ("uploaded once per node (1/P per rank over its own PCIe link, NCCL all-gather "
-                                 "over NVLink)" if shared_csr else "uploaded by every rank")}
+                                 "over NVLink)" if shared_csr else "uploaded by every rank")
+                              + ("" if st.get("uniform_value") is None else
+                                 "; its stored values are all %g (exact host scan every step, 1/P per rank + "
+                                 "one-word all-reduce): filled on the GPU instead of uploaded" % st["uniform_value"])}
     elif with_e2e:
         dist.barrier(); dist.barrier()
         z = torch.zeros(1, dtype=torch.float64, device=dev); dist.all_reduce(z, op=dist.ReduceOp.MAX)

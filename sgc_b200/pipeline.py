@@ -117,27 +117,49 @@ def _host_csr(adj):
             torch.from_numpy(np.ascontiguousarray(m.data, dtype=np.float64)))
 
 
-def _upload_csr_shared(rp_h, col_h, val_h, dev, group):
-    """CSR arrays of a host-resident adjacency onto every GPU of `group` when all ranks need the whole
-    matrix (feature-sharded propagation): each rank pulls 1/P of `col` / `val` over its own PCIe link
-    and an NCCL all-gather over NVLink assembles the full arrays on every GPU -- the replicated upload
-    would move P times the bytes over PCIe (Reddit shape: 280 MB per GPU, 5 ms).  Collective: every
-    rank of the group must call it.  Runs on the current stream."""
+def _shared_piece(nnz, group):
+    """[lo, hi) of the stored entries this rank uploads, and the padded piece length."""
     import torch.distributed as dist
     world, rank = dist.get_world_size(group), dist.get_rank(group)
-    nnz = int(col_h.numel())
     per = max(2, ((nnz + world - 1) // world + 1) // 2 * 2)
-    lo, hi = min(nnz, rank * per), min(nnz, (rank + 1) * per)
-    rp = rp_h.to(dev, non_blocking=True)
-    out = []
-    for host, dtype in ((col_h, torch.int32), (val_h, torch.float64)):
-        piece = torch.zeros(per, dtype=dtype, device=dev)
-        if hi > lo:
-            piece[:hi - lo].copy_(host[lo:hi], non_blocking=True)
-        full = torch.empty(per * world, dtype=dtype, device=dev)
-        dist.all_gather_into_tensor(full, piece, group=group)
-        out.append(full[:nnz])
-    return rp, out[0], out[1]
+    return min(nnz, rank * per), min(nnz, (rank + 1) * per), per, world
+
+
+def _upload_shared(host, dtype, dev, group):
+    """One array of the shared adjacency: this rank's 1/P over its own PCIe link, then an NCCL
+    all-gather over NVLink assembles the whole array on every GPU.  Returns (array, bytes uploaded)."""
+    import torch.distributed as dist
+    nnz = int(host.numel())
+    lo, hi, per, world = _shared_piece(nnz, group)
+    piece = torch.zeros(per, dtype=dtype, device=dev)
+    if hi > lo:
+        piece[:hi - lo].copy_(host[lo:hi], non_blocking=True)
+    full = torch.empty(per * world, dtype=dtype, device=dev)
+    dist.all_gather_into_tensor(full, piece, group=group)
+    return full[:nnz], (hi - lo) * host.element_size()
+
+
+def _uniform_value_shared(val_h, dev, group):
+    """`uniform_value` for an adjacency every rank of `group` holds in host memory: each rank compares
+    its own 1/P of the values with the first one, and a one-word all-reduce (MIN) makes the verdict
+    common -- every rank fills, or every rank uploads and all-gathers (a split decision would leave
+    the all-gather short of participants).  Collective.  No time budget: the piece is small."""
+    import math
+    import torch.distributed as dist
+    if os.environ.get("SGC_B200_UNIFORM_VALUES", "1") == "0":
+        return None
+    nnz = int(val_h.numel())
+    if val_h.dtype != torch.float64 or not val_h.is_contiguous() or val_h.is_cuda or nnz == 0:
+        return None
+    first = float(val_h[0])
+    if not math.isfinite(first):
+        return None
+    lo, hi, _, world = _shared_piece(nnz, group)
+    threads = max(1, host_threads() // world)
+    same = hi <= lo or _ffi.lib().sgc_host_all_equal_f64(val_h.data_ptr() + 8 * lo, hi - lo, first, threads, 0) == 1
+    verdict = torch.tensor([1 if same else 0], dtype=torch.int32, device=dev)
+    dist.all_reduce(verdict, op=dist.ReduceOp.MIN, group=group)
+    return first if int(verdict.item()) == 1 else None
 
 
 def host_threads():
@@ -192,7 +214,9 @@ def precompute_host(adj, features, degree, standardize=False, out=None, out_bloc
               call with their own column block of the features (feature-sharded propagation): the
               adjacency is then uploaded once per node -- 1/P per rank -- and all-gathered over NVLink
     detect_uniform_values   scan the stored values on the host and, when they are all the same, fill the
-              device array instead of uploading it (`uniform_value`); default: on unless `group` is given
+              device array instead of uploading it (`uniform_value`; under `group` every rank scans its
+              own 1/P and a one-word all-reduce makes the verdict common); default: on, except under
+              `group`, where it measured neutral and is opt-in
     stats     optional dict; receives h2d_bytes / d2h_bytes actually copied by this call and
               uniform_value (the fill value, or None when the values were uploaded)
     trace     optional list; receives (label, device ms since the start mark, host ms since the call) for
@@ -260,14 +284,29 @@ def precompute_host(adj, features, degree, standardize=False, out=None, out_bloc
             nbytes = lambda t: t.numel() * t.element_size()
             h2d = nbytes(rp_h) + nbytes(features)
             fill = None
+            # under `group` the scan is opt-in: at N = 2 it measured neutral (16.3 vs 15.7 ms: the piece scan
+            # and the verdict's read-back stall the enqueueing thread for as long as the upload they save)
+            detect = (group is None) if detect_uniform_values is None else bool(detect_uniform_values)
             if group is not None:
-                rp, col, val = _upload_csr_shared(rp_h, col_h, val_h, dev, group)
-                h2d += -(-(nbytes(col_h) + nbytes(val_h)) // torch.distributed.get_world_size(group))
+                # all ranks hold the same adjacency in host memory (feature-sharded propagation): 1/P of
+                # `col` / `val` per rank over its own PCIe link + an NCCL all-gather over NVLink, instead of
+                # P times the bytes over PCIe (Reddit shape: 280 MB per GPU, 5 ms).  Collective.
+                rp = rp_h.to(dev, non_blocking=True)
+                col, up = _upload_shared(col_h, torch.int32, dev, group)
+                h2d += up
+                if detect:
+                    fill = _uniform_value_shared(val_h, dev, group)
+                    mark("values scanned", c_in)
+                if fill is not None:
+                    val = torch.full((val_h.numel(),), fill, dtype=torch.float64, device=dev)
+                else:
+                    val, up = _upload_shared(val_h, torch.float64, dev, group)
+                    h2d += up
             else:
                 rp = rp_h.to(dev, non_blocking=True)
                 col = col_h.to(dev, non_blocking=True)
                 h2d += nbytes(col_h)
-                if detect_uniform_values or detect_uniform_values is None:
+                if detect:
                     ahead = nbytes(col_h)
                     if by_cols:
                         upload_slab(*slabs[0])                 # keeps the DMA engine fed during the host scan

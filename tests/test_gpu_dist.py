@@ -171,12 +171,36 @@ def host_worker(rank, world, port, ret):
         c0, c1 = partition_features(200, world)[rank]
         host = (n, s["row_ptr"].cpu().pin_memory(), s["col"].cpu().pin_memory(), s["val"].cpu().pin_memory())
         xh = x[:, c0:c1].contiguous().cpu().pin_memory()
-        got = sgc_b200.precompute_host(host, xh, k, standardize=True, group=dist.group.WORLD, col_slab=64)
+        st = {}
+        got = sgc_b200.precompute_host(host, xh, k, standardize=True, group=dist.group.WORLD, col_slab=64, stats=st,
+                                       detect_uniform_values=True)
         alone = sgc_b200.precompute_host(host, xh, k, standardize=True, col_slab=64)
         graph = sgc_b200.normalize_csr(n, s["row_ptr"], s["col"], s["val"])
         mean, std = sgc_b200.col_stats(x)
         want, _ = sgc_b200.sgc_precompute(sgc_b200.to_padded((x - mean) / std), graph, k)
-        ret[rank] = (bool(torch.equal(got, alone)), bool(torch.equal(got, want[:, c0:c1].cpu())))
+        ok = [bool(torch.equal(got, alone)), bool(torch.equal(got, want[:, c0:c1].cpu()))]
+        # the constant value array (2.0: adj + adj.T) is recognised piecewise, by consensus, and filled
+        ok.append(st["uniform_value"] == float(host[3][0]))
+        os.environ["SGC_B200_UNIFORM_VALUES"] = "0"           # always upload + all-gather: same bits
+        st0 = {}
+        got0 = sgc_b200.precompute_host(host, xh, k, standardize=True, group=dist.group.WORLD, col_slab=64, stats=st0,
+                                        detect_uniform_values=True)
+        os.environ["SGC_B200_UNIFORM_VALUES"] = "1"
+        ok.append(st0["uniform_value"] is None and bool(torch.equal(got0, got)))
+        ok.append(st0["h2d_bytes"] > st["h2d_bytes"])
+        # a deviation that only the LAST rank's piece holds: every rank must upload (common verdict)
+        val2 = s["val"].clone()
+        val2[-1] = 3.5
+        g2 = sgc_b200.normalize_csr(n, s["row_ptr"], s["col"], val2)
+        want2, _ = sgc_b200.sgc_precompute(sgc_b200.to_padded((x - mean) / std), g2, k)
+        st2 = {}
+        got2 = sgc_b200.precompute_host((n, host[1], host[2], val2.cpu().pin_memory()), xh, k, standardize=True,
+                                        group=dist.group.WORLD, col_slab=64, stats=st2, detect_uniform_values=True)
+        ok.append(st2["uniform_value"] is None and bool(torch.equal(got2, want2[:, c0:c1].cpu())))
+        st3 = {}
+        got3 = sgc_b200.precompute_host(host, xh, k, standardize=True, group=dist.group.WORLD, col_slab=64, stats=st3)
+        ok.append(st3["uniform_value"] is None and bool(torch.equal(got3, got)))      # opt-in under `group`
+        ret[rank] = tuple(ok)
     finally:
         dist.destroy_process_group()
 
@@ -184,10 +208,11 @@ def host_worker(rank, world, port, ret):
 @pytest.mark.parametrize("world", [1, 2])
 def test_host_pipeline_shared_adjacency_upload(world):
     """precompute_host(group=...): every rank uploads 1/P of the adjacency and an NCCL all-gather
-    replicates it; the result equals the rank-local upload and the single-GPU columns bit for bit."""
+    replicates it; the result equals the rank-local upload and the single-GPU columns bit for bit; a
+    constant value array is recognised piecewise (one-word all-reduce) and filled instead."""
     if torch.cuda.device_count() < world:
         pytest.skip("needs %d GPUs" % world)
     ret = mp.Manager().dict()
     mp.spawn(host_worker, args=(world, free_port(), ret), nprocs=world, join=True)
     for rank in range(world):
-        assert ret[rank] == (True, True), (rank, ret[rank])
+        assert ret[rank] == (True,) * 7, (rank, ret[rank])
