@@ -110,3 +110,55 @@ def test_partition_features_and_sharding_choice():
     assert choose_sharding(2449029, 126e6, 100, 8) == "rows"
     assert choose_sharding(111059956, 1.75e9, 128, 8) == "rows"
     assert choose_sharding(232965, 23.4e6, 602, 8, mem_bytes=1e8) == "rows"   # S replica does not fit
+
+
+def shared_worker(rank, world, port, ret):
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from sgc_b200 import pipeline
+        cpu = torch.device("cpu")
+        group = dist.group.WORLD
+        pieces = {}
+        for nnz in (0, 1, 2, 3, 7, 64, 1001, 23163630):
+            lo, hi, per, w = pipeline._shared_piece(nnz, group)
+            pieces[nnz] = (lo, hi, per, w)
+        verdicts = []
+        os.environ["SGC_B200_UNIFORM_VALUES"] = "1"
+        val = torch.full((200001,), 2.0, dtype=torch.float64)
+        verdicts.append(pipeline._uniform_value_shared(val, cpu, group))            # constant -> 2.0 everywhere
+        val[-1] = 3.0                                                                 # only the last rank sees it
+        verdicts.append(pipeline._uniform_value_shared(val, cpu, group))
+        val[-1] = 2.0
+        val[0] = 5.0                                                                  # only the first rank sees it
+        verdicts.append(pipeline._uniform_value_shared(val, cpu, group))
+        val[0] = float("inf")
+        verdicts.append(pipeline._uniform_value_shared(val, cpu, group))
+        val[0] = 2.0
+        verdicts.append(pipeline._uniform_value_shared(val.float(), cpu, group))    # not fp64: never scanned
+        verdicts.append(pipeline._uniform_value_shared(val[:1], cpu, group))        # one entry, empty pieces elsewhere
+        os.environ["SGC_B200_UNIFORM_VALUES"] = "0"
+        verdicts.append(pipeline._uniform_value_shared(val, cpu, group))
+        ret[rank] = (pieces, verdicts)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_shared_adjacency_pieces_and_common_verdict(world):
+    """pipeline._shared_piece tiles the stored entries (even piece length: 16-byte aligned fp64 / 8-byte
+    int32 pieces); pipeline._uniform_value_shared gives every rank the same verdict whichever rank's
+    piece holds the deviation (gloo, verdict tensor on the CPU; the scan itself is host code)."""
+    import __graft_entry__ as entry
+    entry.build()
+    ret = mp.Manager().dict()
+    mp.spawn(shared_worker, args=(world, free_port(), ret), nprocs=world, join=True)
+    for nnz in ret[0][0]:
+        spans = [ret[r][0][nnz] for r in range(world)]
+        per = spans[0][2]
+        assert all(s[2] == per and s[3] == world for s in spans) and per % 2 == 0 and per * world >= nnz
+        assert spans[0][0] == 0 and spans[-1][1] == nnz
+        assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
+        assert all(0 <= hi - lo <= per for lo, hi, _, _ in spans)
+    for r in range(world):
+        assert ret[r][1] == [2.0, None, None, None, None, 2.0, None], (r, ret[r][1])
