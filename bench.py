@@ -211,6 +211,9 @@ def workload_config(name, n, nnz, f, k, **extra):
     cfg = {"workload": label, "nodes": n, "nnz_S": nnz, "features": f, "k_hops": k,
            "l2_hygiene": "inputs larger than L2 (X %.0f MB + CSR %.0f MB vs 126 MB L2); no flush"
                          % (n * f * 4 / 1e6, nnz * 12 / 1e6)}
+    if name == "reddit":
+        cfg["choice"] = ("largest single-GPU configuration of BASELINE.json and the one SURVEY 8(d) sets the target on; "
+                         "configs[1] (Pubmed: X = 39 MB, L2-resident, launch-bound) is other_workloads.pubmed")
     cfg.update(extra)
     return cfg
 
