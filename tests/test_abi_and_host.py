@@ -270,3 +270,25 @@ def test_textsgc_and_sparse_feature_entry_points_have_no_cpu_path():
     for fn in (textsgc.preprocess_adj, textsgc.normalize_adj, sparse_features.row_normalize):
         with pytest.raises(_ffi.SgcError):
             fn(a)
+
+
+def test_bench_reference_arm_contract():
+    """`bench.py --impl reference` (the reference's CPU path on a bounded sample): exactly one JSON
+    line on stdout with the contract's keys; ranks other than 0 print nothing and exit 0."""
+    import json
+    env = dict(os.environ, SGC_BENCH_CPU_FRACTION="64", CUDA_VISIBLE_DEVICES="")
+    cmd = [sys.executable, os.path.join(REPO, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0"]
+    r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [l for l in r.stdout.splitlines() if l.strip()]
+    assert len(lines) == 1, lines
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["value"] > 0 and d["unit"] == "edge*feat/s" and d["higher_is_better"] is True
+    assert d["steps"] == 1 and d["warmup"] == 0 and d["n_gpus"] == 1 and d["gpu_launches"] == 0
+    assert d["config"]["workload"].startswith("Reddit-shaped") and "model" not in d["config"]
+    assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] >= 1 and d["cpu_baseline"]["sample"]
+    assert d["cpu_baseline"]["value"] == d["value"] == d["e2e"]["value"]
+    assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["d2h_bytes_per_step"] == 0
+    r = subprocess.run(cmd + ["--gpus", "2"], env=dict(env, RANK="1", WORLD_SIZE="2", LOCAL_RANK="1"),
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and r.stdout.strip() == ""
