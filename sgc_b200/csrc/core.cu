@@ -239,10 +239,20 @@ int32_t sgc_host_all_equal_f64(const double *v, int64_t n, double value, int32_t
     if (t <= 1) { scan(0, n); return state.load(); }
     const int64_t per = (n + t - 1) / t;
     std::vector<std::thread> pool;
-    pool.reserve((size_t)t - 1);
+    try {
+        pool.reserve((size_t)t - 1);
+    } catch (...) {
+        scan(0, n);
+        return state.load();
+    }
     for (int64_t k = 1; k < t; ++k) {
         const int64_t lo = k * per, hi = lo + per < n ? lo + per : n;
-        if (lo < hi) pool.emplace_back(scan, lo, hi);
+        if (lo >= hi) continue;
+        try {
+            pool.emplace_back(scan, lo, hi);
+        } catch (...) {                                // no more threads to be had: this piece inline
+            scan(lo, hi);
+        }
     }
     scan(0, per < n ? per : n);
     for (auto &th : pool) th.join();
