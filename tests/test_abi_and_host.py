@@ -292,3 +292,34 @@ def test_bench_reference_arm_contract():
     r = subprocess.run(cmd + ["--gpus", "2"], env=dict(env, RANK="1", WORLD_SIZE="2", LOCAL_RANK="1"),
                        capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and r.stdout.strip() == ""
+
+
+def test_row_blocks_cover_rows_and_balance_entries():
+    """pipeline.row_blocks: row-slice views of one CSR (shared col / value arrays, sliced row_ptr),
+    128-row aligned cuts, balanced by stored entries rather than rows (power-law graphs)."""
+    from sgc_b200 import pipeline
+    from sgc_b200.graph import SgcGraph
+    rng = np.random.default_rng(5)
+    n = 5000
+    deg = np.minimum((rng.pareto(1.2, n) * 3).astype(np.int64) + 1, 900)
+    deg[:40] = 900                                            # hubs first: equal row counts would be unbalanced
+    row_ptr = torch.from_numpy(np.concatenate(([0], np.cumsum(deg))).astype(np.int64))
+    nnz = int(row_ptr[-1])
+    col = torch.from_numpy(rng.integers(0, n, nnz).astype(np.int32))
+    sval = torch.ones(nnz, dtype=torch.float32)
+    g = SgcGraph(n, n, row_ptr, col, None, None, sval=sval)
+    assert [(a, b) for a, b, _ in pipeline.row_blocks(g, 1)] == [(0, n)] and pipeline.row_blocks(g, 1)[0][2] is g
+    for nb in (2, 3, 8, 64):
+        blocks = pipeline.row_blocks(g, nb)
+        assert 1 <= len(blocks) <= nb
+        assert blocks[0][0] == 0 and blocks[-1][1] == n
+        assert all(a[1] == b[0] for a, b in zip(blocks, blocks[1:]))
+        sizes = []
+        for r0, r1, sub in blocks:
+            assert r1 > r0 and (r0 % 128 == 0) and sub.n_rows == r1 - r0 and sub.n_cols == n
+            assert sub.col.data_ptr() == col.data_ptr() and sub.sval.data_ptr() == sval.data_ptr()
+            assert torch.equal(sub.row_ptr, row_ptr[r0:r1 + 1])          # offsets into the shared arrays
+            sizes.append(int(row_ptr[r1] - row_ptr[r0]))
+        assert sum(sizes) == nnz
+        if nb <= 8:
+            assert max(sizes) <= nnz // nb + 128 * 900                    # within one aligned cut of the target
