@@ -1,16 +1,23 @@
 #!/usr/bin/env python
 """Benchmark of the SGC feature-propagation hot path (BASELINE.json metric: K-hop propagation
-edge*feat/s and achieved HBM GB/s vs roofline).
+edge*feat/s and achieved GB/s vs roofline).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload NAME]
 
-One "step" = one `sgc_precompute` (K hops of S X with the D^-1/2 scaling and, for the Reddit
-shape, the feature standardisation fused into the first hop) on synthetic inputs of the named
-BASELINE shape.  N=1 workload: configs[2], the Reddit-shaped graph (232,965 nodes, ~23M nnz,
-602 features, K=2) -- the configuration north_star's roofline target is quoted on.  Prints ONE
-JSON line (rank 0).  See DESIGN.md "Measurement" for the definitions of every key.
+One "step" = one `sgc_precompute` (K hops of S X on device-resident CSR + standardised X: the span the
+reference times at utils.py:93-96) on synthetic inputs of the named BASELINE shape.  N=1 workload:
+configs[2], the Reddit-shaped graph (232,965 nodes, ~23M nnz, 602 features, K=2) -- the configuration
+north_star's roofline target is quoted on.  The normalisation (K1/K2), the column statistics and the
+in-place standardisation (K3) are timed separately (`details`) and are inside `e2e`.  Prints ONE JSON
+line (rank 0).  See DESIGN.md "Measurement" for the definitions of every key.
+
+`--impl reference`: the UNMODIFIED reference (baseline/_ref, staged by tools/stage_reference.sh) on the
+host cores -- its own aug_normalized_adjacency, sparse_mx_to_torch_sparse_tensor and sgc_precompute; it
+imports nothing of this repo's package and never touches a GPU.
 """
 import argparse
+import contextlib
+import importlib.util
 import json
 import os
 import sys
@@ -24,14 +31,26 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-from sgc_b200 import synth  # noqa: E402
-
 METRIC = "K-hop propagation edge*feat/s (sgc_precompute)"
 UNIT = "edge*feat/s"
+REF_DIR = os.path.join(ROOT, "baseline", "_ref")
+TOLERANCE = "|a-b| <= 1e-6 + 1e-5*|b| (north_star: 1e-5 relative / 1e-6 absolute per element)"
 
 
 def env_int(name, default):
     return int(os.environ.get(name, default))
+
+
+def load_synth():
+    """sgc_b200/synth.py loaded by path: the input generator is pure torch, and loading it this way keeps
+    the reference arm free of the package (and of libsgc_b200.so)."""
+    mod = sys.modules.get("_sgc_synth")
+    if mod is None:
+        spec = importlib.util.spec_from_file_location("_sgc_synth", os.path.join(ROOT, "sgc_b200", "synth.py"))
+        mod = importlib.util.module_from_spec(spec)
+        sys.modules["_sgc_synth"] = mod
+        spec.loader.exec_module(mod)
+    return mod
 
 
 def peaks():
@@ -43,11 +62,15 @@ def peaks():
 
 
 def ncu_traffic(workload):
-    """dram bytes per hop launch from the committed ncu --set full capture, if there is one."""
+    """Per-launch counters of the hop kernel from the committed `ncu --set full` capture of this workload
+    (profiles/roofline_traffic.json: dram bytes, L2 hit rate, the capture's file and date), or None."""
     path = os.path.join(ROOT, "profiles", "roofline_traffic.json")
     if os.path.exists(path):
         with open(path) as fh:
-            return json.load(fh).get(workload)
+            v = json.load(fh).get(workload)
+        if isinstance(v, (int, float)):
+            return {"dram_bytes": int(v)}
+        return v
     return None
 
 
@@ -56,6 +79,11 @@ def hop_bytes(n, nnz, f):
     int32 column, one fp32 weight and one F-float row of X; per row one F-float store and one
     int64 row pointer."""
     return nnz * (4 + 4 + 4 * f) + 4 * f * n + 8 * (n + 1)
+
+
+def compulsory_bytes(n, nnz, f):
+    """Every array once (SURVEY 8d B_min): col + value per entry, row pointers, X read, Y written."""
+    return 8 * nnz + 8 * (n + 1) + 8 * f * n
 
 
 class ClockSampler(threading.Thread):
@@ -108,114 +136,262 @@ class ClockSampler(threading.Thread):
                 "reasons": sorted(self.reasons), "samples": len(self.samples)}
 
 
-def make_workload(name, device, scale=1.0):
-    s = synth.make_shape(name, device=device, scale=scale)
-    return s
-
-
-# --------------------------------------------------------------------------------------------------
-def cpu_reference_rate(s_csr_host, x_host, mean, std, rows, reps, threads):
-    """The reference's own CPU implementation of the path (oracle/reference_port.py: torch.spmm on
-    a torch sparse tensor built like utils.py:23-30) on the first `rows` rows of S; returns
-    (edge*feat/s, seconds per rep, nnz in the sample)."""
-    from oracle import reference_port as rp
-    import scipy.sparse as sp
-    torch.set_num_threads(threads)
-    indptr, indices, data = s_csr_host
-    sub = sp.csr_matrix((data[:indptr[rows]], indices[:indptr[rows]], indptr[:rows + 1]),
-                        shape=(rows, x_host.shape[0]))
-    adj = rp.sparse_mx_to_torch_sparse_tensor(sub)
-    x = torch.from_numpy(x_host)
-    if mean is not None:
-        x = (x - torch.from_numpy(mean)) / torch.from_numpy(std)      # utils.py:119 (outside the timed hops)
-    rp.sgc_precompute(x, adj, 1)                                       # warm-up
-    best = []
-    for _ in range(reps):
-        _, secs = rp.sgc_precompute(x, adj, 1)
-        best.append(secs)
-    secs = float(np.median(best))
-    nnz = int(indptr[rows])
-    return nnz * x_host.shape[1] / secs, secs, nnz
-
-
-def host_copies(graph, x):
-    """Host (pinned) copies of S in CSR fp32 and of X, for the CPU arms."""
-    indptr = graph.row_ptr.cpu().numpy()
-    indices = graph.col.cpu().numpy()
-    data = graph.values32().cpu().numpy()
-    return (indptr, indices, data), x.cpu().numpy()
-
-
-def run_reference(args):
-    """--impl reference: the reference's CPU path (torch.spmm, all host threads) on the same
-    config; each step is a bounded sample (a slab of rows of one hop)."""
-    rank = int(os.environ.get("RANK", "0"))
-    if rank != 0:
-        return
-    import sgc_b200
-    name = args.workload
-    threads = os.cpu_count() or 1
-    if torch.cuda.is_available():
-        dev = torch.device("cuda", 0)
-        s = make_workload(name, dev)
-        graph = sgc_b200.normalize_csr(s["n"], s["row_ptr"], s["col"], s["val"])
-        csr, x_host = host_copies(graph, s["x"])
-        n, f, k, nnz = s["n"], s["f"], s["k"], graph.nnz
-        del graph, s
-        torch.cuda.empty_cache()
-    else:  # no GPU: build S with the reference's own host code
-        from oracle import reference_port as rp
-        import scipy.sparse as sp
-        s = make_workload(name, "cpu")
-        a = sp.csr_matrix((s["val"].numpy(), s["col"].numpy(), s["row_ptr"].numpy()), shape=(s["n"], s["n"]))
-        S = rp.aug_normalized_adjacency(a).tocsr()
-        S.sort_indices()
-        csr = (S.indptr.astype(np.int64), S.indices.astype(np.int32), S.data.astype(np.float32))
-        x_host = s["x"].numpy()
-        n, f, k, nnz = s["n"], s["f"], s["k"], S.nnz
-    from oracle import reference_port as rp
-    import scipy.sparse as sp
-    rows = max(1, n // env_int("SGC_BENCH_CPU_FRACTION", 16))
-    torch.set_num_threads(threads)
-    indptr, indices, data = csr
-    sub = sp.csr_matrix((data[:indptr[rows]], indices[:indptr[rows]], indptr[:rows + 1]), shape=(rows, n))
-    adj = rp.sparse_mx_to_torch_sparse_tensor(sub)
-    x = torch.from_numpy(x_host)
-    if name == "reddit":
-        x = rp.standardize(x)
-    for _ in range(args.warmup):
-        rp.sgc_precompute(x, adj, 1)
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        rp.sgc_precompute(x, adj, 1)
-    secs = (time.perf_counter() - t0) / args.steps
-    sample_nnz = int(indptr[rows])
-    value = sample_nnz * f / secs
-    sample = "rows [0,%d) of one hop (%d of %d stored entries), torch.spmm fp32" % (rows, sample_nnz, nnz)
-    line = {
-        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": secs * 1e3, "higher_is_better": True,
-        "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(name, n, nnz, f, k),
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
-        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0,
-    }
-    print(json.dumps(line))
-
-
-def workload_config(name, n, nnz, f, k, **extra):
+def workload_config(name, n, nnz, f, k):
+    """`config` of the JSON line: names the workload and nothing else, so that both arms (and every N)
+    print the same object; measurements and schedule descriptions live in `details`."""
     label = {"reddit": "Reddit-shaped synthetic inductive SGC K=2 (BASELINE configs[2])",
              "products": "ogbn-products-shaped synthetic power-law graph K=3 (BASELINE configs[3])",
              "papers100m": "ogbn-papers100M-shaped synthetic K=3 (BASELINE configs[4])"}[name]
-    cfg = {"workload": label, "nodes": n, "nnz_S": nnz, "features": f, "k_hops": k,
+    cfg = {"workload": label, "nodes": int(n), "nnz_S": int(nnz), "features": int(f), "k_hops": int(k),
            "l2_hygiene": "inputs larger than L2 (X %.0f MB + CSR %.0f MB vs 126 MB L2); no flush"
                          % (n * f * 4 / 1e6, nnz * 12 / 1e6)}
     if name == "reddit":
         cfg["choice"] = ("largest single-GPU configuration of BASELINE.json and the one SURVEY 8(d) sets the target on; "
                          "configs[1] (Pubmed: X = 39 MB, L2-resident, launch-bound) is other_workloads.pubmed")
-    cfg.update(extra)
     return cfg
+
+
+# --------------------------------------------------------------------------------------------------
+# The reference's CPU implementation of the path
+class Reference(object):
+    """The reference's own functions for this path.  kind == "reference": the unmodified files staged
+    under baseline/_ref (normalization.py, utils.py), imported as they are; kind == "port":
+    oracle/reference_port.py, only when nothing is staged (the same calls, restated)."""
+
+    def __init__(self):
+        if os.path.exists(os.path.join(REF_DIR, "utils.py")) and os.path.exists(os.path.join(REF_DIR, "normalization.py")):
+            saved = {k: sys.modules.pop(k) for k in ("utils", "normalization") if k in sys.modules}
+            sys.path.insert(0, REF_DIR)
+            try:
+                import normalization as ref_norm
+                import utils as ref_utils
+            finally:
+                sys.path.remove(REF_DIR)
+                for k in ("utils", "normalization"):
+                    sys.modules.pop(k, None)
+                sys.modules.update(saved)
+            for mod in (ref_norm, ref_utils):
+                assert os.path.dirname(os.path.abspath(mod.__file__)) == REF_DIR, mod.__file__
+            self.kind = "reference"
+            self.where = "baseline/_ref (unmodified normalization.py + utils.py of the reference)"
+            self.aug_normalized_adjacency = ref_norm.aug_normalized_adjacency
+            self.to_torch_sparse = ref_utils.sparse_mx_to_torch_sparse_tensor
+            self.sgc_precompute = ref_utils.sgc_precompute
+        else:
+            from oracle import reference_port as rp
+            self.kind = "port"
+            self.where = "oracle/reference_port.py (baseline/_ref is not staged: run tools/stage_reference.sh)"
+            self.aug_normalized_adjacency = rp.aug_normalized_adjacency
+            self.to_torch_sparse = rp.sparse_mx_to_torch_sparse_tensor
+            self.sgc_precompute = rp.sgc_precompute
+
+    def adjacency(self, a_scipy):
+        """utils.py:120-122: adj_normalizer(adj) -> sparse_mx_to_torch_sparse_tensor(adj).float()"""
+        import warnings
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            return self.to_torch_sparse(self.aug_normalized_adjacency(a_scipy)).float()
+
+    @staticmethod
+    def standardize(x):
+        """utils.py:119, the reference's expression (it sits inside load_reddit_data, not callable alone)."""
+        return (x - x.mean(dim=0)) / x.std(dim=0)
+
+
+def host_graph(s):
+    """scipy CSR of A from the synthetic workload dict (host tensors)."""
+    import scipy.sparse as sp
+    return sp.csr_matrix((s["val"].numpy(), s["col"].numpy(), s["row_ptr"].numpy()), shape=(s["n"], s["n"]))
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU path on the same config.  Every step is one call of the
+    unmodified utils.sgc_precompute(X, adj, K) on the WHOLE workload (all rows, all stored entries, all
+    feature columns) -- torch.spmm's cost on the CPU has a large per-call part (it sorts/coalesces the COO
+    tensor the reference's loader builds, every hop), so a row or column sample would misstate the rate.
+    A whole step takes ~10-20 s on the host cores; when steps+warmup of them exceed the time budget
+    (SGC_BENCH_REF_BUDGET_S, default 150 s) fewer whole steps are timed and the line says so: `steps` is the
+    number actually timed, `details.steps_requested` what the command asked for."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    os.environ["CUDA_VISIBLE_DEVICES"] = ""             # this arm never touches a GPU
+    ref = Reference()
+    synth = load_synth()
+    name = args.workload
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    t0 = time.perf_counter()
+    s = synth.make_shape(name, device="cpu", scale=float(os.environ.get("SGC_BENCH_SCALE", "1")))
+    n, f, k = s["n"], s["f"], s["k"]
+    gen_s = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    adj = ref.adjacency(host_graph(s))
+    normalise_s = time.perf_counter() - t0
+    nnz = int(adj._nnz())
+    x = s["x"]
+    t0 = time.perf_counter()
+    if synth.SHAPES[name]["scaled"]:
+        x = ref.standardize(x)
+    standardise_s = time.perf_counter() - t0
+    del s
+
+    budget = float(os.environ.get("SGC_BENCH_REF_BUDGET_S", "150"))
+    warm_times = []
+    for _ in range(min(args.warmup, 1)):                 # one whole step; more warm-up is pointless at ~10 s a step
+        _, secs = ref.sgc_precompute(x, adj, k)
+        warm_times.append(secs)
+    steps = args.steps
+    if warm_times and warm_times[0] * steps > budget:
+        steps = max(1, int(budget / warm_times[0]))
+    total, times = 0.0, []
+    for _ in range(steps):
+        _, secs = ref.sgc_precompute(x, adj, k)
+        total += secs
+        times.append(secs)
+    secs = total / steps
+    value = k * nnz * f / secs
+    sample = ("every step = utils.sgc_precompute(X, adj, %d) on the whole workload (%d rows, %d stored entries of S, "
+              "%d columns), torch.spmm fp32 on %d threads; %d whole steps timed (%d requested, %.0f s budget), "
+              "%d warm-up" % (k, n, nnz, f, threads, steps, args.steps, budget, len(warm_times)))
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": steps, "warmup": len(warm_times), "ms_per_step": secs * 1e3, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(name, n, nnz, f, k),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": ref.kind, "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+        "details": {
+            "code": ref.where,
+            "steps_requested": args.steps, "warmup_requested": args.warmup, "time_budget_s": budget,
+            "step_ms": [round(v * 1e3, 1) for v in times], "warmup_ms": [round(v * 1e3, 1) for v in warm_times],
+            "outside_the_timed_steps_s": {"synthetic_inputs": gen_s,
+                                          "aug_normalized_adjacency+sparse_mx_to_torch_sparse_tensor": normalise_s,
+                                          "standardise (utils.py:119)": standardise_s},
+            "whole_path_s": normalise_s + standardise_s + secs,
+        },
+    }
+    print(json.dumps(line))
+
+
+# --------------------------------------------------------------------------------------------------
+# Checks of the GPU output against the reference's CPU arithmetic (the checker, never the timed path)
+def allclose_report(got, want):
+    """north_star tolerance, element-wise; got / want: host fp32 tensors of one shape."""
+    diff = (got.double() - want.double()).abs()
+    bad = diff > (1e-6 + 1e-5 * want.double().abs())
+    return {"elements": int(want.numel()), "violations": int(bad.sum().item()),
+            "max_abs_diff": float(diff.max().item()) if diff.numel() else 0.0,
+            "bit_identical_elements": int((got == want).sum().item()), "tolerance": TOLERANCE}
+
+
+def sampled_rows_check(ref, graph, x_in, y_out, rows):
+    """Rows `rows` (sorted int64 device tensor) of one hop output y_out = S x_in, recomputed on the CPU by
+    the reference's torch.spmm from the GPU's own operand: the sampled rows of S become a small sparse
+    matrix over the columns they touch (ascending order kept, so torch.spmm accumulates every element in
+    the same sequential order), built by the reference's sparse_mx_to_torch_sparse_tensor."""
+    import scipy.sparse as sp
+    rp = graph.row_ptr
+    beg, end = rp[rows], rp[rows + 1]
+    lens = (end - beg)
+    tot = int(lens.sum().item())
+    seg = torch.repeat_interleave(torch.arange(rows.numel(), device=rows.device), lens)
+    starts = torch.cumsum(lens, 0) - lens
+    pos = beg[seg] + (torch.arange(tot, device=rows.device) - starts[seg])
+    cols = graph.col[pos].long()
+    vals = graph.values32()[pos]
+    uniq, inv = torch.unique(cols, sorted=True, return_inverse=True)
+    indptr = np.concatenate(([0], np.cumsum(lens.cpu().numpy()))).astype(np.int64)
+    sub = sp.csr_matrix((vals.cpu().numpy(), inv.cpu().numpy().astype(np.int64), indptr),
+                        shape=(rows.numel(), uniq.numel()))
+    import warnings
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        adj = ref.to_torch_sparse(sub)
+    want, _ = ref.sgc_precompute(x_in[uniq].float().cpu().contiguous(), adj, 1)
+    rep = allclose_report(y_out[rows].cpu(), want)
+    rep.update(rows=int(rows.numel()), stored_entries=tot)
+    return rep
+
+
+def sample_rows(n, count, device, seed=7):
+    g = torch.Generator(device="cpu")
+    g.manual_seed(seed)
+    return torch.sort(torch.randperm(n, generator=g)[:min(count, n)])[0].to(device)
+
+
+def hopwise_parity(ref, graph, x, k, y_timed, count=1500):
+    """Hop 1 and hop K of the timed K-hop output on sampled rows (the intermediate operand is recomputed by
+    the same deterministic kernels, so it is bit-identical to what the timed step consumed)."""
+    import sgc_b200
+    rows = sample_rows(graph.n_rows, count, graph.device)
+    h1 = sgc_b200.hop(graph, x)
+    out = {"hop1": sampled_rows_check(ref, graph, x, h1, rows)}
+    if k > 1:
+        prev = h1 if k == 2 else sgc_b200.propagate.propagate(graph, x, k - 1)
+        out["hop%d" % k] = sampled_rows_check(ref, graph, prev, y_timed, rows)
+    out["ok"] = all(v["violations"] == 0 for v in out.values() if isinstance(v, dict))
+    out["checker"] = "the reference's torch.spmm on CPU (%s) on %d sampled rows per hop" % (ref.kind, rows.numel())
+    return out
+
+
+def reference_leg(ref, s, name, k, y_gpu):
+    """cpu_baseline + full-size parity in one go (rank 0, N=1): the reference's whole path on the host --
+    its aug_normalized_adjacency on the raw A, utils.py:119 on the raw X, ONE whole K-hop
+    utils.sgc_precompute (timed) -- and its output compared element by element with the GPU output the
+    timed steps produced from the same raw inputs through this repo's K1/K2/K3/K4."""
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    host = {kk: s[kk].cpu() for kk in ("row_ptr", "col", "val")}
+    host["n"] = s["n"]
+    adj = ref.adjacency(host_graph(host))
+    x = s["x"].cpu()
+    synth = load_synth()
+    if synth.SHAPES[name]["scaled"]:
+        x = ref.standardize(x)
+    nnz, f = int(adj._nnz()), int(x.shape[1])
+    ref.sgc_precompute(x[:, :8].contiguous(), adj, 1)           # thread pool / page warm-up, 1 % of a step
+    want, secs = ref.sgc_precompute(x, adj, k)
+    cpu = {"value": k * nnz * f / secs, "unit": UNIT, "cores": threads, "kind": ref.kind,
+           "sample": "ONE whole K=%d step (all %d rows, %d stored entries, %d columns) of utils.sgc_precompute, "
+                     "torch.spmm fp32 on CPU, %.2f s; code: %s" % (k, s["n"], nnz, f, secs, ref.where)}
+    parity = allclose_report(y_gpu.cpu(), want)
+    parity["ok"] = parity["violations"] == 0
+    parity["what"] = ("the timed GPU output S^K X (K1+K2 normalisation, K3 standardisation, K hops, all on the GPU "
+                      "from the raw inputs) vs the %s's whole CPU path on the same raw inputs, all %d x %d elements"
+                      % (ref.kind, s["n"], f))
+    return cpu, parity
+
+
+# --------------------------------------------------------------------------------------------------
+def measure_l2_peak(dev):
+    """L2 -> SM read bandwidth of this box, measured now (sgc_l2_read_probe): best of the two access
+    orders over L2-resident buffers of 32 and 64 MB, CUDA events."""
+    from sgc_b200 import _ffi
+    best = None
+    sink = torch.zeros(1, dtype=torch.float32, device=dev)
+    for mb in (32, 64):
+        buf = torch.ones(mb * 1024 * 1024 // 4, dtype=torch.float32, device=dev)
+        for pattern in (0, 1):
+            reps = 40
+            call = lambda: _ffi.call("sgc_l2_read_probe", buf.data_ptr(), buf.numel() * 4, reps, pattern, 8,
+                                     sink.data_ptr(), torch.cuda.current_stream().cuda_stream)
+            call()
+            torch.cuda.synchronize()
+            ts = []
+            for _ in range(3):
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record(); call(); b.record()
+                torch.cuda.synchronize()
+                ts.append(a.elapsed_time(b))
+            gbs = buf.numel() * 4 * reps / (min(ts) * 1e-3) / 1e9
+            if best is None or gbs > best["gbs"]:
+                best = {"gbs": gbs, "buffer_mb": mb, "order": "address" if pattern == 0 else "hashed"}
+        del buf
+    best["how"] = ("sgc_l2_read_probe: every warp reads 512-byte pieces (ld.global.nc.L1::no_allocate.v4) of an "
+                   "L2-resident buffer, 8 CTAs x 256 threads per SM, 40 passes, best of 3, CUDA events; measured in this run")
+    return best
 
 
 def run_own(args):
@@ -239,8 +415,9 @@ def run_own(args):
         from sgc_b200 import dist as sgc_dist
         return sgc_dist.bench(args, rank, world, dev, globals())
 
+    synth = load_synth()
     name = args.workload
-    s = make_workload(name, dev)
+    s = synth.make_shape(name, device=dev)
     n, f, k = s["n"], s["f"], s["k"]
     torch.cuda.synchronize()
     # ---- one-off preparation, timed separately (K1 + K2, K3) ----
@@ -258,9 +435,12 @@ def run_own(args):
     graph, normalise_ms = timed(lambda: sgc_b200.normalize_csr(n, s["row_ptr"], s["col"], s["val"]))
     # features in the layout the loaders produce (utils.load_reddit_data): padded row stride
     x = sgc_b200.to_padded(s["x"])
+    if x.data_ptr() == s["x"].data_ptr():
+        x = x.clone()                       # s["x"] stays raw for the reference leg
     mean32 = std32 = x_raw = None
     stats_ms = standardise_ms = 0.0
-    if name == "reddit":
+    scaled = synth.SHAPES[name]["scaled"]
+    if scaled:
         (mean32, std32), stats_ms = timed(lambda: sgc_b200.col_stats(x))
         x_raw = sgc_b200.features.padded_rows(n, f, dev)   # raw copy kept for the fused-hop variants below
         x_raw.copy_(x)
@@ -307,11 +487,11 @@ def run_own(args):
 
     ybuf = sgc_b200.features.padded_rows(n, f, dev)
     hop_ms = {"plain": hop_time(lambda: sgc_b200.hop(graph, x, out=ybuf))}
-    if name == "reddit":
+    if scaled and not args.skip_variants:
         for mode in ("rcp", "div"):
             hop_ms["fused_std_" + mode] = hop_time(
                 lambda: sgc_b200.hop(graph, x_raw, mean=mean32, std=std32, std_mode=mode, out=ybuf))
-    del x_raw
+    del x_raw, ybuf
     incumbent = None
     if not args.skip_incumbent:
         try:
@@ -319,38 +499,31 @@ def run_own(args):
         except Exception as exc:        # reported for context only: never costs the primary line
             incumbent = {"error": repr(exc)[:300]}
         torch.cuda.empty_cache()
-    peak, peak_src = peaks()
-    b_hop = hop_bytes(n, nnz, f)
-    avg_launch_s = ms_per_step * 1e-3 / k
-    achieved = b_hop / avg_launch_s / 1e9
-    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": ncu_traffic(name), "peak_source": peak_src, "kernel": "spmm_hop_kernel",
-                "algorithmic_bytes_per_launch": b_hop,
-                "compulsory_bytes_per_launch": 12 * nnz + 8 * (n + 1) + 8 * f * n,
-                "hop_ms": hop_ms}
+    roofline = roofline_block(name, n, nnz, f, ms_per_step / k, dev)
+    roofline["hop_ms"] = hop_ms
+
+    # ---- the reference's CPU path on this box's host cores + parity of the timed output ----
+    cpu = parity = None
+    if not args.no_cpu_baseline:
+        ref = Reference()
+        cpu, parity = reference_leg(ref, s, name, k, y)
+        parity["sampled_rows_per_hop"] = hopwise_parity(ref, graph, x, k, y)
+        if not (parity["ok"] and parity["sampled_rows_per_hop"]["ok"]):
+            print(json.dumps({"error": "GPU output differs from the reference beyond tolerance", "parity": parity}),
+                  file=sys.stderr)
+            sys.exit(3)
 
     # ---- end to end through the public API with HOST buffers ----
     e2e = None if args.skip_e2e else run_e2e(args, s, name, k, nnz, dev)
 
-    # ---- the reference's CPU path on this box's host cores (bounded sample) ----
-    cpu = None
-    if not args.no_cpu_baseline:
-        csr, x_host = host_copies(graph, x)
-        threads = os.cpu_count() or 1
-        rows = max(1, n // env_int("SGC_BENCH_CPU_FRACTION", 8))
-        rate, secs, sample_nnz = cpu_reference_rate(csr, x_host, None, None, rows, 3, threads)
-        cpu = {"value": rate, "unit": UNIT, "cores": threads, "kind": "port",
-               "sample": "rows [0,%d) of one hop (%d of %d stored entries), torch.spmm fp32 on CPU, median of 3 (%.2f s each)"
-                         % (rows, sample_nnz, nnz, secs)}
-
     # ---- the other single-GPU-sized BASELINE config, for the 1/2/4/8-GPU series (not the headline) ----
     others = {}
     extra_names = os.environ.get("SGC_BENCH_EXTRA", "products" if not args.workload_given else "")
-    del graph, x, y, ybuf, s
+    del graph, x, y, s
     torch.cuda.empty_cache()
     for other in [e for e in extra_names.split(",") if e and e != name]:
         try:
-            others[other] = single_gpu_extra(other, dev, peak)
+            others[other] = single_gpu_extra(other, dev, check=not args.no_cpu_baseline)
         except Exception as exc:        # an optional extra must never cost the primary line
             others[other] = {"error": repr(exc)[:300]}
 
@@ -364,21 +537,62 @@ def run_own(args):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(name, n, nnz, f, k, normalise_ms=normalise_ms, normalise_first_call_ms=normalise_cold_ms,
-                                  col_stats_ms=stats_ms,
-                                  standardise_inplace_ms=standardise_ms,
-                                  chunk=sgc_b200.propagate.default_chunk(),
-                                  weights=("fp32((d_i*a_ij)*d_j) formed in the hop kernel (SGC_B200_FUSED_NORM=1)"
-                                           if sgc_b200.propagate.fused_norm() else
-                                           "fp32 S values written once by sgc_norm_values (inside normalise_ms, outside "
-                                           "the timed hops like the reference's normalisation), streamed by every hop"),
-                                  timed_region="K hops on device-resident CSR + standardised X, as "
-                                               "utils.py:93-96 times them; K1/K2/K3 + standardisation "
-                                               "timed separately (above) and inside e2e"),
+        "config": workload_config(name, n, nnz, f, k),
         "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+        "parity": parity,
+        "details": {
+            "normalise_ms": normalise_ms, "normalise_first_call_ms": normalise_cold_ms,
+            "col_stats_ms": stats_ms, "standardise_inplace_ms": standardise_ms,
+            "chunk": sgc_b200.propagate.default_chunk(),
+            "weights": ("fp32((d_i*a_ij)*d_j) formed in the hop kernel (SGC_B200_FUSED_NORM=1)"
+                        if sgc_b200.propagate.fused_norm() else
+                        "fp32 S values written once by sgc_norm_values (inside normalise_ms, outside "
+                        "the timed hops like the reference's normalisation), streamed by every hop"),
+            "timed_region": "K hops on device-resident CSR + standardised X, as utils.py:93-96 times them; "
+                            "K1/K2 (normalise_ms), K3 (col_stats_ms + standardise_inplace_ms: one exact in-place "
+                            "pass, NOT fused into hop 1 -- measured slower, see roofline.hop_ms.fused_std_*) are "
+                            "timed separately here and are inside e2e"},
         "gpu_incumbent": incumbent, "other_workloads": others,
     }
     print(json.dumps(line))
+
+
+def roofline_block(name, n, nnz, f, hop_ms, dev, per_gpu_fraction=1.0, l2=True):
+    """`roofline` of the hop kernel.  The hop is a gather: its algorithmic bytes (SURVEY 8d gather model)
+    are served by L2 wherever a row of X is re-read, by DRAM otherwise.  bound = "l2" when a feature slab of
+    X is L2-resident (Reddit shape: the kernel is limited by the L2 -> SM path, its DRAM traffic is a
+    fraction of the algorithmic bytes), "hbm" when X is far larger than L2 (products / papers shapes)."""
+    hbm, hbm_src = peaks()
+    b_hop = hop_bytes(n, nnz, f) * per_gpu_fraction
+    b_min = compulsory_bytes(n, nnz, f) * per_gpu_fraction
+    secs = hop_ms * 1e-3
+    gather = b_hop / secs / 1e9
+    slab_resident = n * min(f, 32) * 4 <= 128 * 1024 * 1024
+    cap = ncu_traffic(name) if per_gpu_fraction == 1.0 else None
+    dram = {"peak": hbm, "peak_source": hbm_src, "unit": "GB/s",
+            "compulsory_bytes_per_launch": b_min, "compulsory_frac": b_min / secs / 1e9 / hbm}
+    traffic = None
+    if cap:
+        traffic = cap.get("dram_bytes")
+        dram.update(achieved=traffic / secs / 1e9, frac=traffic / secs / 1e9 / hbm,
+                    traffic_over_compulsory=traffic / b_min, capture=cap)
+    out = {"kernel": "spmm_hop_kernel", "unit": "GB/s", "algorithmic_bytes_per_launch": b_hop,
+           "gather_model_gbs": gather, "traffic": traffic, "dram": dram}
+    if slab_resident and l2:
+        peak = measure_l2_peak(dev)
+        out.update(bound="l2", achieved=gather, peak=peak["gbs"], frac=gather / peak["gbs"],
+                   peak_source="L2 -> SM read bandwidth measured in this run (sgc_l2_read_probe)", l2=dict(
+                       achieved=gather, peak=peak["gbs"], frac=gather / peak["gbs"], probe=peak,
+                       note="achieved = gather-model bytes / hop time: the bytes the SMs pull through L2 (ncu "
+                            "l1tex__m_xbar2l1tex_read_bytes of the committed capture agrees within 3 %)"))
+        out["frac_of_hbm_peak_gather_model"] = gather / hbm
+    else:
+        # X does not stay in L2: the kernel is DRAM-bound; the fraction is real DRAM traffic over the copy peak
+        # when a capture exists, else the gather model (an upper bound on the traffic the kernel may cause)
+        ach = dram.get("achieved", gather)
+        out.update(bound="hbm", achieved=ach, peak=hbm, frac=ach / hbm, peak_source=hbm_src,
+                   achieved_is="ncu dram bytes / hop time" if "achieved" in dram else "gather-model bytes / hop time")
+    return out
 
 
 def gpu_incumbent(graph, x, f, hop_time, ours_ms):
@@ -398,10 +612,12 @@ def gpu_incumbent(graph, x, f, hop_time, ours_ms):
             "note": "torch.spmm(COO) is what utils.py:95 runs on a GPU in the reference; library calls, reported only"}
 
 
-def single_gpu_extra(name, dev, peak):
-    """K hops of another named workload on this one GPU (device-timed, 3 warm-ups + 5 steps)."""
+def single_gpu_extra(name, dev, check=True):
+    """K hops of another named workload on this one GPU (device-timed, 3 warm-ups + 5 steps), with the
+    DRAM-side roofline and a sampled-row check of the timed output against the reference's torch.spmm."""
     import sgc_b200
-    s = make_workload(name, dev)
+    synth = load_synth()
+    s = synth.make_shape(name, device=dev)
     n, f, k = s["n"], s["f"], s["k"]
     graph = sgc_b200.normalize_csr(n, s["row_ptr"], s["col"], s["val"])
     x = sgc_b200.to_padded(s["x"])
@@ -412,16 +628,16 @@ def single_gpu_extra(name, dev, peak):
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     a.record()
     for _ in range(5):
-        sgc_b200.propagate.propagate(graph, x, k)
+        y = sgc_b200.propagate.propagate(graph, x, k)
     b.record()
     torch.cuda.synchronize()
     ms = a.elapsed_time(b) / 5
     nnz = graph.nnz
-    achieved = k * hop_bytes(n, nnz, f) / (ms * 1e-3) / 1e9
     out = {"workload": workload_config(name, n, nnz, f, k)["workload"], "n_gpus": 1, "value": k * nnz * f / (ms * 1e-3),
-           "unit": UNIT, "ms_per_step": ms, "nnz_S": nnz,
-           "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak}}
-    del graph, x
+           "unit": UNIT, "ms_per_step": ms, "nnz_S": nnz, "roofline": roofline_block(name, n, nnz, f, ms / k, dev)}
+    if check:
+        out["parity"] = hopwise_parity(Reference(), graph, x, k, y)
+    del graph, x, y
     torch.cuda.empty_cache()
     return out
 
@@ -432,6 +648,7 @@ def pubmed_extra(dev):
     golden vectors were generated with (ind.pubmed.allx is missing from the reference snapshot).
     X (39 MB) fits L2: the hops are launch/latency-bound, reported for completeness."""
     import sgc_b200
+    synth = load_synth()
     g = np.load(os.path.join(ROOT, "tests", "golden", "pubmed.npz"), allow_pickle=False)
     n = g["adj_indptr"].size - 1
     graph = sgc_b200.normalize_csr(n, *(torch.from_numpy(np.ascontiguousarray(g["adj_" + kk])).to(dev)
@@ -454,12 +671,29 @@ def pubmed_extra(dev):
             "matches_reference_sha256": bool(ok), "l2_hygiene": "X (39 MB) is L2-resident: warm-cache, launch-bound"}
 
 
+@contextlib.contextmanager
+def env_override(**kw):
+    old = {k: os.environ.get(k) for k in kw}
+    os.environ.update({k: str(v) for k, v in kw.items()})
+    try:
+        yield
+    finally:
+        for k, v in old.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+
+
 def run_e2e(args, s, name, k, nnz_s, dev):
     """Same metric through the reference-facing API with host buffers: every step uploads the raw
     adjacency (CSR of A) and the raw features from pinned host memory, normalises on the GPU
     (K1+K2), computes the column statistics (K3), runs the K hops and reads the propagated
-    features back to pinned host memory."""
+    features back to pinned host memory.  Measured twice: with the exact host scan that recognises a
+    constant-valued adjacency (the reference's loaders only produce those) and fills its value array on the
+    GPU, and with the scan off (`weighted_adjacency`: what an adjacency with real weights costs)."""
     import sgc_b200
+    synth = load_synth()
     n, f = s["n"], s["f"]
     host = {kk: s[kk].cpu().pin_memory() for kk in ("row_ptr", "col", "val", "x")}
     out_host = torch.empty((n, f), dtype=torch.float32).pin_memory()
@@ -469,28 +703,41 @@ def run_e2e(args, s, name, k, nnz_s, dev):
         # sgc_b200.precompute_host: CSR(A) up first, K1/K2 overlap the upload of X, the last hop runs
         # by row blocks whose D2H overlaps the next block (sgc_b200/pipeline.py)
         sgc_b200.precompute_host((n, host["row_ptr"], host["col"], host["val"]), host["x"], k,
-                                 standardize=(name == "reddit"), out=out_host, stats=stats)
+                                 standardize=bool(synth.SHAPES[name]["scaled"]), out=out_host, stats=stats)
 
     widths = sgc_b200.pipeline.slab_widths(f, sgc_b200.pipeline.default_col_slab(n, f))
     schedule = ("column slabs of %s floats, strided 2-D DMA copies" % "+".join(str(w) for w in widths)
                 if len(widths) > 1 else
                 "one contiguous copy; last hop in %d row blocks" % sgc_b200.pipeline.default_out_blocks())
     steps = max(2, min(args.steps, 5))
-    step()
-    t0 = time.perf_counter()
-    for _ in range(steps):
+
+    def measure():
         step()
-    secs = (time.perf_counter() - t0) / steps
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            step()
+        return (time.perf_counter() - t0) / steps
+
+    secs = measure()
+    st = dict(stats)
+    with env_override(SGC_B200_UNIFORM_VALUES="0"):
+        secs_w = measure()
+    st_w = dict(stats)
     host_bytes = sum(t.numel() * t.element_size() for t in host.values())
     values = ("the %d stored values of A are all %g (adj + adj.T of a 0/1 matrix, utils.py:116; found by a threaded "
               "exact scan on the host, inside the timed region, every step): filled on the GPU instead of uploaded "
               "-- %d of the %d input bytes cross PCIe"
-              % (host["val"].numel(), stats["uniform_value"], stats["h2d_bytes"], host_bytes)) \
-        if stats["uniform_value"] is not None else \
+              % (host["val"].numel(), st["uniform_value"], st["h2d_bytes"], host_bytes)) \
+        if st["uniform_value"] is not None else \
         "all %d input bytes cross PCIe" % host_bytes
-    return {"value": k * nnz_s * f / secs, "unit": UNIT, "h2d_bytes_per_step": int(stats["h2d_bytes"]),
-            "d2h_bytes_per_step": int(stats["d2h_bytes"]), "ms_per_step": secs * 1e3, "steps": steps,
+    return {"value": k * nnz_s * f / secs, "unit": UNIT, "h2d_bytes_per_step": int(st["h2d_bytes"]),
+            "d2h_bytes_per_step": int(st["d2h_bytes"]), "ms_per_step": secs * 1e3, "steps": steps,
             "host_input_bytes": int(host_bytes),
+            "weighted_adjacency": {"value": k * nnz_s * f / secs_w, "ms_per_step": secs_w * 1e3,
+                                   "h2d_bytes_per_step": int(st_w["h2d_bytes"]),
+                                   "what": "same call with SGC_B200_UNIFORM_VALUES=0: the value array of A is "
+                                           "uploaded like any weighted adjacency's"},
+            "scan_gave_up": bool(st.get("scan_gave_up", False)),
             "path": "sgc_b200.precompute_host: pinned host CSR(A)+X -> H2D (row_ptr + col first; X in %s; %s) -> "
                     "aug_normalized_adjacency (K1,K2, overlapped with the upload of X) -> per slab: col_stats + "
                     "standardise (K3), K hops, strided D2H into the pinned host result while the next slab is "
@@ -504,9 +751,11 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="own", choices=["own", "reference"])
     ap.add_argument("--workload", default=None, choices=[None, "reddit", "products", "papers100m"])
-    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true",
+                    help="profiling runs only: skips the reference's CPU leg and the parity check it feeds")
     ap.add_argument("--skip-e2e", action="store_true", help="profiling runs only: leaves e2e null")
     ap.add_argument("--skip-incumbent", action="store_true", help="do not time torch.spmm / cuSPARSE beside the hop")
+    ap.add_argument("--skip-variants", action="store_true", help="do not time the fused-standardisation hop variants")
     args = ap.parse_args()
     args.workload_given = args.workload is not None
     if args.workload is None:

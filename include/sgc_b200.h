@@ -57,6 +57,14 @@ int64_t sgc_launch_count(void);
  * device maximum; the granted size is written to granted_out (may be NULL).  Process-wide. */
 int32_t sgc_l2_set_persisting_bytes(int64_t bytes, int64_t *granted_out);
 
+/* Measurement aid (bench.py `roofline.l2`, tools/l2_peak.py): reads the `bytes` (multiple of 512) at buf_d
+ * `reps` times from all SMs in 512-byte pieces (32 lanes x 16 bytes, the hop kernel's gather shape) with L1
+ * allocation off -- with a buffer that stays resident in the 126 MB L2 the CUDA-event time of this launch is
+ * the L2 -> SM read bandwidth of the box.  pattern 0: pieces in address order, 1: hashed order.  sink_d: one
+ * float the kernel may write (keeps the loads alive).  No counterpart in the reference. */
+int32_t sgc_l2_read_probe(const void *buf_d, int64_t bytes, int32_t reps, int32_t pattern,
+                          int32_t ctas_per_sm, float *sink_d, void *stream);
+
 /* ---- column-slab transfers (utils.py:82-88,126-130: the reference's .cuda() / .cpu() copies) -------
  * Strided 2-D copy on the DMA engines (cudaMemcpy2DAsync, direction inferred from the pointers):
  * `rows` pieces of `width_bytes` each, `src_pitch_bytes` / `dst_pitch_bytes` apart.  Moves one
@@ -219,6 +227,11 @@ int32_t sgc_spmm_plan_tag_hot(sgc_plan_t *plan, int64_t hot_rows, int32_t *col_t
 #define SGC_HOP_FUSED_NORM   1u   /* weights = fp32((d_i*a_ij)*d_j) on the fly from aval_d + dinv_d */
 #define SGC_HOP_STD_DIV      2u   /* gathered x -> (x - mean[f]) / std[f]   (exact, utils.py:119)   */
 #define SGC_HOP_STD_RCP      4u   /* gathered x -> (x - mean[f]) * (1/std[f])  (<= 1 ulp from DIV)   */
+#define SGC_HOP_PAD_OWNED    8u   /* columns [f, round_up(f, 4)) of y_d (and of every peer_y_d) are padding
+                                     that belongs to the operand (ldy >= round_up(f, 4)): the hop may cover
+                                     them with whole-vector stores (they receive zeros when the pad columns
+                                     of x are zero).  Without the flag nothing beyond column f-1 is written,
+                                     so y_d may be a column view of a wider live matrix.                */
 
 typedef struct sgc_hop_args {
     const double *aval_d;      /* FUSED_NORM: fp64 values of A+I (pruned structure)          */
@@ -241,14 +254,17 @@ typedef struct sgc_hop_args {
                                   plan's hot-column tags (sgc_spmm_plan_tag_hot) if it has them;
                                   measurement aids for the multi-GPU hop: bit3 run the peer variant
                                   but skip the pushes (results on peers are then stale), bit4 push
-                                  with per-lane stores instead of cp.async.bulk                  */
+                                  with per-lane stores instead of cp.async.bulk, bit5 never merge the
+                                  rows of a tile into one bulk store, bit6 end the kernel after the
+                                  source reads of the bulk stores instead of their completion    */
     /* Row-sharded multi-GPU hop (K5): every output row is ALSO stored, from the registers of the
      * SpMM epilogue, to the same (row, column) offset of n_peers other buffers -- the peers'
      * copies of the gathered operand of the next hop, mapped into this process with
      * sgc_ipc_open() and reached over NVLink.  peer_y_d[p] corresponds to y_d (same logical row
      * 0, same leading dimension ldy).  n_peers = 0 for a single-GPU hop. */
     int32_t       n_peers;
-    int32_t       reserved_;
+    int32_t       push_tile_tasks; /* consecutive tasks per group slot whose rows travel as one bulk store
+                                      when they are contiguous in y (0 = default 8; rows per tile <= 32)  */
     float        *peer_y_d[SGC_MAX_PEERS];
     /* Optional halo mask, one uint32 per row of this hop (n_rows entries): bit p set = peer p's
      * shard gathers this row in the next hop, so it must be pushed to peer_y_d[p]; clear = peer p

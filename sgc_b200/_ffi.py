@@ -16,6 +16,7 @@ c_i32, c_i64, c_u32, c_sz, c_p = (ctypes.c_int32, ctypes.c_int64, ctypes.c_uint3
 HOP_FUSED_NORM = 1
 HOP_STD_DIV = 2
 HOP_STD_RCP = 4
+HOP_PAD_OWNED = 8
 MAX_PEERS = 15
 IPC_HANDLE_BYTES = 64
 
@@ -29,7 +30,7 @@ class HopArgs(ctypes.Structure):
         ("partial_d", c_p), ("ldp", c_i64),
         ("mean_d", c_p), ("std_d", c_p),
         ("f", c_i32), ("slab_floats", c_i32), ("flags", c_u32), ("hints", c_i32),
-        ("n_peers", c_i32), ("reserved_", c_i32), ("peer_y_d", c_p * 15),
+        ("n_peers", c_i32), ("push_tile_tasks", c_i32), ("peer_y_d", c_p * 15),
         ("peer_mask_d", c_p),
     ]
 
@@ -41,6 +42,7 @@ SIGNATURES = {
     "sgc_device_check": (c_i32, [c_i32]),
     "sgc_launch_count": (c_i64, []),
     "sgc_l2_set_persisting_bytes": (c_i32, [c_i64, ctypes.POINTER(c_i64)]),
+    "sgc_l2_read_probe": (c_i32, [c_p, c_i64, c_i32, c_i32, c_i32, c_p, c_p]),
     "sgc_copy_2d": (c_i32, [c_p, c_i64, c_p, c_i64, c_i64, c_i64, c_p]),
     "sgc_host_all_equal_f64": (c_i32, [c_p, c_i64, ctypes.c_double, c_i32, c_i64]),
     "sgc_scan_workspace_bytes": (c_sz, [c_i64]),

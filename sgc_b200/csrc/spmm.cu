@@ -243,7 +243,10 @@ static int32_t run_hop(const sgc_plan_impl *pl, const sgc_hop_args_t *a, const f
     p.f = a->f; p.chunk = pl->chunk;
     p.n_slabs = (a->f + slab - 1) / slab;
     p.y_vec = y_vec;
-    p.hints = a->hints & (3 | 8 | 16);
+    // whole-vector stores may spill into columns [f, round4(f)) only when the caller owns them as padding
+    const bool pad_owned = (flags & SGC_HOP_PAD_OWNED) != 0 && (a->f + 3) / 4 * 4 <= ldy;
+    p.f_store = pad_owned ? (a->f + 3) / 4 * 4 : a->f;
+    p.hints = a->hints & (3 | 8 | 16 | 32 | 64);
     // keeping gathered rows with evict_last only helps when the slab can actually stay in L2
     if (!slab_fits_l2(pl->n_cols, slab < a->f ? slab : a->f)) p.hints &= ~1;
     SGC_REQUIRE(a->n_peers >= 0 && a->n_peers <= SGC_MAX_PEERS, "spmm_hop: n_peers out of range");
@@ -257,6 +260,18 @@ static int32_t run_hop(const sgc_plan_impl *pl, const sgc_hop_args_t *a, const f
         // the bulk-store path assumes the peers' copies are laid out like y (same alignment)
         SGC_REQUIRE(y_vec != 4 || (reinterpret_cast<uintptr_t>(a->peer_y_d[i]) & 15) == 0,
                     "spmm_hop: peer_y_d[%d] must be 16-byte aligned like y_d", i);
+    }
+    if (p.n_peers > 0) {
+        SGC_REQUIRE(y_vec != 4 || a->f % 4 == 0 || pad_owned,
+                    "spmm_hop: peer pushes of a width that is not a multiple of 4 floats need SGC_HOP_PAD_OWNED "
+                    "(the bulk stores cover the pad columns)");
+        // rows per tile: push_tile_tasks tasks per group slot (default 8), at most 32 rows per warp tile
+        const int gpw = 32 / g;
+        int tpw = a->push_tile_tasks > 0 ? a->push_tile_tasks : 8;
+        if (tpw * gpw > 32) tpw = 32 / gpw;
+        p.tpw = tpw;
+        // tiles are contiguous in y when one slab covers the whole padded row
+        p.stage_stride = (p.n_slabs == 1 && ldy <= slab && y_vec == 4) ? (int32_t)ldy : slab;
     }
     const int64_t n_tasks = (int64_t)p.n_slabs * (p.n_long_items + p.n_rows);
     int32_t rc = fn(p, n_tasks, s);
@@ -471,7 +486,9 @@ int32_t sgc_precompute(const sgc_plan_t *plan, const sgc_hop_args_t *args, int32
         const bool last = (k == k_hops - 1);
         float *dst = last ? args->y_d : ((k & 1) ? buf_b_d : buf_a_d);
         const int64_t ld_dst = last ? args->ldy : ld_buf;
-        const uint32_t flags = (k == 0) ? args->flags : (args->flags & ~std_bits);
+        uint32_t flags = (k == 0) ? args->flags : (args->flags & ~std_bits);
+        // the ping-pong buffers are this call's own padded storage; the last hop writes the caller's y
+        flags = last ? flags : (flags | SGC_HOP_PAD_OWNED);
         int32_t rc = run_hop_auto(&plan->impl, args, src, ld_src, dst, ld_dst, flags, false, s);
         if (rc != SGC_OK) return rc;
         src = dst;

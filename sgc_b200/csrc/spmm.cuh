@@ -26,7 +26,6 @@
 namespace sgc {
 
 constexpr int HOP_THREADS = 128;
-__host__ __device__ constexpr int hop_tasks_per_warp(bool peers) { return peers ? 4 : 1; }
 
 struct HopDev {
     const int64_t *row_ptr;
@@ -53,6 +52,10 @@ struct HopDev {
     int32_t n_slabs;
     int32_t y_vec;       // widest legal vector store into y (1, 2 or 4 floats)
     int32_t hints;       // bit0: L2 evict_last on gathered rows; bit1: evict_first on streams
+    int32_t f_store;     // columns [0, f_store) of y may be written with whole vectors (f rounded up only when
+                         // the pad columns belong to the operand; else == f and tails go element-wise)
+    int32_t tpw;         // K5: tasks per tile and group slot of the peer variant (rows per tile = tpw * 32/G)
+    int32_t stage_stride;// K5: floats between staged rows (ldy when tiles are contiguous in y, else the slab width)
     int32_t n_peers;     // K5: copies of y in other GPUs' memory that receive every output row
     float *peer_y[SGC_MAX_PEERS];
     const uint32_t *peer_mask;   // per-row bit set of peers that need the row (null: all)
@@ -182,34 +185,32 @@ __device__ __forceinline__ float standardize(float x, float mu, float s)
     return x;
 }
 
+// One task of the hop: a group of G lanes accumulates one (row or chunk item) x (feature slab) piece in
+// registers and stores it to y / the partial-sum scratch.  Returns what the peer epilogue needs.
+template <int G, int VEC, int U>
+struct TaskOut {
+    float acc[U][VEC];
+    int fo[U];
+    bool act[U];
+    int64_t row;
+    int f0;
+    int sv;
+    bool valid, to_y;
+};
+
 // HOT: p.col carries a tag in bit 31 ("this column is among the most frequently gathered ones");
 // tagged rows of X are loaded with an L2 evict_last policy, all others with evict_first, which
 // pins the hub rows in L2 when X as a whole is far larger than L2.
-template <int G, int VEC, int U, bool FUSED, int STD, bool PEERS, bool HOT>
-__global__ void __launch_bounds__(HOP_THREADS, PEERS ? 7 : 5)
-spmm_hop_kernel(const HopDev p)
+template <int G, int VEC, int U, bool FUSED, int STD, bool HOT>
+__device__ __forceinline__ void hop_task(const HopDev &p, const int64_t task, const int lane, const uint64_t pol_x,
+                                         const uint64_t pol_hot, const uint64_t pol_s, TaskOut<G, VEC, U> &o)
 {
     constexpr int GPW = 32 / G;                       // tasks per warp
     constexpr int SW = G * VEC * U;                   // slab width in floats
     constexpr int UNR = (U * VEC >= 8) ? 4 : 8;       // gathers in flight per lane
     static_assert(G % UNR == 0, "unroll must divide the group size");
-
-    // The peer variant walks TPW consecutive tasks per warp so that the NVLink pushes of one row
-    // drain while the next row is being gathered (see the epilogue).
-    constexpr int TPW = hop_tasks_per_warp(PEERS);
-
-    const int lane = threadIdx.x & 31;
     const int gl = lane % G;
-    const int64_t warp = (int64_t)blockIdx.x * (HOP_THREADS / 32) + (threadIdx.x >> 5);
     const int64_t per_slab = p.n_long_items + p.n_rows;
-
-    const uint64_t pol_x = l2_policy(HOT ? 2 : ((p.hints & 1) ? 1 : 0));    // HOT: policy of untagged rows
-    const uint64_t pol_hot = l2_policy(1);
-    const uint64_t pol_s = l2_policy((p.hints & 2) ? 2 : 0);
-
-#pragma unroll 1
-    for (int it = 0; it < TPW; ++it) {
-    const int64_t task = (warp * TPW + it) * GPW + lane / G;
     const int64_t slab = task / per_slab;
     const int64_t t = task - slab * per_slab;
 
@@ -235,31 +236,29 @@ spmm_hop_kernel(const HopDev p)
     if (!valid) beg = end = 0;
 
     const int f0 = (int)slab * SW;
-    int fo[U], fo_ld[U];
-    bool act[U];
+    int fo_ld[U];
     float mu[U][VEC], sg[U][VEC];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
-        fo[u] = f0 + (u * G + gl) * VEC;
-        act[u] = valid && fo[u] < p.f;
-        fo_ld[u] = act[u] ? fo[u] : 0;
+        o.fo[u] = f0 + (u * G + gl) * VEC;
+        o.act[u] = valid && o.fo[u] < p.f;
+        fo_ld[u] = o.act[u] ? o.fo[u] : 0;
 #pragma unroll
         for (int v = 0; v < VEC; ++v) {
             mu[u][v] = 0.f;
             sg[u][v] = 1.f;
-            if (STD != 0 && act[u] && fo[u] + v < p.f) {
-                mu[u][v] = p.mean[fo[u] + v];
-                const float s = p.stdv[fo[u] + v];
+            if (STD != 0 && o.act[u] && o.fo[u] + v < p.f) {
+                mu[u][v] = p.mean[o.fo[u] + v];
+                const float s = p.stdv[o.fo[u] + v];
                 sg[u][v] = (STD == 2) ? __frcp_rn(s) : s;
             }
         }
     }
 
-    float acc[U][VEC];
 #pragma unroll
     for (int u = 0; u < U; ++u)
 #pragma unroll
-        for (int v = 0; v < VEC; ++v) acc[u][v] = 0.f;
+        for (int v = 0; v < VEC; ++v) o.acc[u][v] = 0.f;
 
     const double di = (FUSED && valid) ? p.dinv_rows[row] : 0.0;
     const int len = (int)(end - beg);
@@ -315,9 +314,9 @@ spmm_hop_kernel(const HopDev p)
                     for (int u = 0; u < U; ++u)
 #pragma unroll
                         for (int v = 0; v < VEC; ++v)
-                            acc[u][v] = __fmaf_rn(wj[jj],
-                                                  standardize<STD>(xv[jj][u].v[v], mu[u][v], sg[u][v]),
-                                                  acc[u][v]);
+                            o.acc[u][v] = __fmaf_rn(wj[jj],
+                                                    standardize<STD>(xv[jj][u].v[v], mu[u][v], sg[u][v]),
+                                                    o.acc[u][v]);
                 }
             }
         }
@@ -328,109 +327,220 @@ spmm_hop_kernel(const HopDev p)
     if (valid) {
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-            if (!act[u]) continue;
-            float *q = dst + fo[u];
-            if (VEC == 4 && sv == 4) {
-                st_hint_v4(q, acc[u], pol_y);
-            } else if (VEC >= 2 && sv >= 2) {
+            if (!o.act[u]) continue;
+            float *q = dst + o.fo[u];
+            if (VEC == 4 && sv == 4 && o.fo[u] + 4 <= p.f_store) {
+                st_hint_v4(q, o.acc[u], pol_y);
+            } else if (VEC >= 2 && sv >= 2 && o.fo[u] + VEC <= p.f_store) {
 #pragma unroll
-                for (int v = 0; v < VEC; v += 2)
-                    if (fo[u] + v < p.f) st_hint_v2(q + v, &acc[u][v], pol_y);
+                for (int v = 0; v < VEC; v += 2) st_hint_v2(q + v, &o.acc[u][v], pol_y);
             } else {
 #pragma unroll
                 for (int v = 0; v < VEC; ++v)
-                    if (fo[u] + v < p.f) st_hint_v1(q + v, acc[u][v], pol_y);
+                    if (o.fo[u] + v < p.f) st_hint_v1(q + v, o.acc[u][v], pol_y);
             }
         }
     }
-    if constexpr (PEERS) {
-    if (p.n_peers <= 0 || (p.hints & 8)) continue;     // hints bit 3: measurement aid, no push
-    // K5: every output row also goes to each peer's copy of the next hop's gathered operand, inside
-    // this kernel, while other warps are still gathering.
-    // Fast path (16-byte aligned output): the group's piece of the row is staged in shared memory in
-    // feature order and ONE lane hands it to the TMA unit -- a cp.async.bulk shared -> global per
-    // peer -- so the LSU never waits on NVLink and the fabric sees whole-row writes (measured 8 GPUs
-    // all-to-all: 640-680 GB/s per GPU against 544 GB/s for per-lane 16-byte stores).
-    if (p.y_vec == 4 && !(p.hints & 16)) {               // hints bit 4: force the per-lane store path
-        // Two staging buffers per warp: the bulk stores of task `it` keep reading buffer it&1 while
-        // task it+1 is gathered; before a buffer is overwritten, its issuing lane waits until at
-        // most the newer group is still reading (wait_group.read 1).
-        __shared__ __align__(128) float stage[HOP_THREADS / 32][2][32 * VEC * U];
-        float *mine = stage[threadIdx.x >> 5][it & 1] + (lane / G) * SW;
-        const bool push = valid && to_y;
-        if (gl == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
-        __syncwarp();
-        if (push) {
-#pragma unroll
-            for (int u = 0; u < U; ++u)
-#pragma unroll
-                for (int v = 0; v < VEC; ++v) mine[(u * G + gl) * VEC + v] = act[u] ? acc[u][v] : 0.f;
+    o.row = row; o.f0 = f0; o.sv = sv; o.valid = valid; o.to_y = to_y;
+}
+
+template <int G, int VEC, int U, bool FUSED, int STD, bool HOT>
+__global__ void __launch_bounds__(HOP_THREADS, 5)
+spmm_hop_kernel(const HopDev p)
+{
+    constexpr int GPW = 32 / G;
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = (int64_t)blockIdx.x * (HOP_THREADS / 32) + (threadIdx.x >> 5);
+    const uint64_t pol_x = l2_policy(HOT ? 2 : ((p.hints & 1) ? 1 : 0));    // HOT: policy of untagged rows
+    const uint64_t pol_hot = l2_policy(1);
+    const uint64_t pol_s = l2_policy((p.hints & 2) ? 2 : 0);
+    TaskOut<G, VEC, U> o;
+    hop_task<G, VEC, U, FUSED, STD, HOT>(p, warp * GPW + lane / G, lane, pol_x, pol_hot, pol_s, o);
+}
+
+// K5: the hop with the NVLink exchange fused in.  Every output row also goes to each peer's copy of the next
+// hop's gathered operand, inside this kernel, while other warps are still gathering.
+//
+// Persistent grid (one wave of CTAs); a warp walks TILES of RT = tpw * GPW consecutive tasks.  The output
+// rows of a tile are staged in shared memory and handed to the TMA unit as cp.async.bulk shared -> global
+// stores, so the LSU never waits on NVLink:
+//   * tile store: when the tile is RT consecutive rows of y, all computed here, and a peer needs all of
+//     them, ONE bulk store of RT * ldy * 4 bytes goes to that peer (rows are contiguous in the operand,
+//     pad columns included).  Measured 8-GPU all-to-all: 416-byte stores 578 GB/s per GPU, 1.6 KB 641,
+//     8 KB 670 (profiles/r01_nvlink_probe_n8_products.log) -- row-sized stores were the limiter of the
+//     first version of this kernel (491 GB/s inside the hop);
+//   * row store: otherwise each lane l < RT pushes row l of the tile, piece by piece, to the peers whose
+//     halo mask asks for it.
+// Two staging buffers per warp: the stores of tile i keep reading buffer i&1 while tile i+1 is gathered;
+// before a buffer is overwritten every lane waits until at most the newer group is still being read
+// (wait_group.read 1).  Before the warp exits every lane waits for full COMPLETION of its stores
+// (cp.async.bulk.wait_group 0, not .read): the writes have been performed at the peers when the grid
+// completes, and the stream-ordered barrier that follows the kernel (dist.py) publishes them.
+template <int G, int VEC, int U, bool FUSED, bool HOT>
+__global__ void __launch_bounds__(HOP_THREADS, 6)
+spmm_hop_peers_kernel(const HopDev p, const int64_t n_tiles)
+{
+    constexpr int GPW = 32 / G;
+    constexpr int SW = G * VEC * U;
+    constexpr int WARPS = HOP_THREADS / 32;
+    const int lane = threadIdx.x & 31;
+    const int gl = lane % G;
+    const int wic = threadIdx.x >> 5;
+    const int64_t warp = (int64_t)blockIdx.x * WARPS + wic;
+    const int64_t n_warps = (int64_t)gridDim.x * WARPS;
+    const uint64_t pol_x = l2_policy(HOT ? 2 : ((p.hints & 1) ? 1 : 0));
+    const uint64_t pol_hot = l2_policy(1);
+    const uint64_t pol_s = l2_policy((p.hints & 2) ? 2 : 0);
+    const int R = p.tpw;                       // tasks per tile and group slot
+    const int RT = R * GPW;                    // rows (tasks) per tile, <= 32
+    const int stride = p.stage_stride;         // floats between staged rows: ldy (tile-capable) or SW
+    const bool bulk = p.y_vec == 4 && !(p.hints & 16);
+    const bool tile_capable = bulk && stride == (int)p.ldy && !(p.hints & 32);
+
+    extern __shared__ __align__(128) float stage_all[];
+    __shared__ int32_t row_s[WARPS][32];       // local row of each staged slot, -1: nothing to push
+    float *stage_w = stage_all + (size_t)wic * 2 * RT * stride;
+    const int64_t per_slab = p.n_long_items + p.n_rows;
+
+    int iter = 0;
+#pragma unroll 1
+    for (int64_t tile = warp; tile < n_tiles; tile += n_warps, ++iter) {
+        float *buf = stage_w + (size_t)(iter & 1) * RT * stride;
+        if (bulk) {
+            asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+            __syncwarp();
         }
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        __syncwarp();
-        if (push && gl == 0) {
-            int nfl = p.f - f0;
-            nfl = nfl > SW ? SW : nfl;
-            const uint32_t bytes = (uint32_t)((nfl + 3) & ~3) * 4u;       // pad columns lie inside ldy
-            const uint32_t src = (uint32_t)__cvta_generic_to_shared(mine);
-            const int64_t off = row * p.ldy + f0;
-            const uint32_t need = p.peer_mask ? __ldg(p.peer_mask + row) : 0xffffffffu;
-            for (int pp = 0; pp < p.n_peers; ++pp)
-                if ((need >> pp) & 1u)
-                    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
-                                 :: "l"(p.peer_y[pp] + off), "r"(src), "r"(bytes) : "memory");
-        }
-        // every leader commits one (possibly empty) group per task, so "1 pending" always means
-        // "the previous task's stores"
-        if (gl == 0) asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-        if (it == TPW - 1 && gl == 0)
-            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // smem dies with the CTA
-        continue;
-    }
-    if (!valid) continue;
-    // Fallback for unaligned outputs: fire-and-forget per-lane stores from the registers.
-    if (to_y) {
-        const int64_t off = row * p.ldy;
-        const uint32_t need = p.peer_mask ? __ldg(p.peer_mask + row) : 0xffffffffu;
-        for (int pp = 0; pp < p.n_peers; ++pp) {
-            if (!((need >> pp) & 1u)) continue;
-            float *base = p.peer_y[pp] + off;
+        const int64_t t0 = tile * RT;
+        // RT consecutive rows of y: all tasks are row tasks of one slab (long-row chunk items come first)
+        bool whole = tile_capable && (t0 % per_slab) >= p.n_long_items && (t0 % per_slab) + RT <= per_slab;
+        uint32_t need_and = 0xffffffffu;
+        int64_t first_row = 0;
+        int f0_tile = 0;
+#pragma unroll 1
+        for (int it = 0; it < R; ++it) {
+            TaskOut<G, VEC, U> o;
+            hop_task<G, VEC, U, FUSED, 0, HOT>(p, t0 + it * GPW + lane / G, lane, pol_x, pol_hot, pol_s, o);
+            if (p.n_peers <= 0 || (p.hints & 8)) continue;     // hints bit 3: measurement aid, no push
+            const bool push = o.valid && o.to_y;
+            if (bulk) {
+                const int slot = it * GPW + lane / G;
+                float *mine = buf + (size_t)slot * stride;
+                if (push) {
 #pragma unroll
-            for (int u = 0; u < U; ++u) {
-                if (!act[u]) continue;
-                float *q = base + fo[u];
-                if (VEC == 4 && sv == 4) {
-                    st_peer_v4(q, acc[u]);
-                } else if (VEC >= 2 && sv >= 2) {
+                    for (int u = 0; u < U; ++u) {
+                        const int c = (u * G + gl) * VEC;
+                        if (c < stride) {
 #pragma unroll
-                    for (int v = 0; v < VEC; v += 2)
-                        if (fo[u] + v < p.f) st_peer_v2(q + v, &acc[u][v]);
-                } else {
+                            for (int v = 0; v < VEC; ++v) mine[c + v] = o.act[u] ? o.acc[u][v] : 0.f;
+                        }
+                    }
+                }
+                if (gl == 0) row_s[wic][slot] = push ? (int32_t)o.row : -1;
+                whole = whole && __all_sync(0xffffffffu, push);
+                if (it == 0) { first_row = __shfl_sync(0xffffffffu, o.row, 0); f0_tile = __shfl_sync(0xffffffffu, o.f0, 0); }
+                if (p.peer_mask && push && gl == 0) need_and &= __ldg(p.peer_mask + o.row);
+            } else if (push) {
+                // unaligned outputs: fire-and-forget per-lane stores from the registers
+                const int64_t off = o.row * p.ldy;
+                const uint32_t need = p.peer_mask ? __ldg(p.peer_mask + o.row) : 0xffffffffu;
+                for (int pp = 0; pp < p.n_peers; ++pp) {
+                    if (!((need >> pp) & 1u)) continue;
+                    float *base = p.peer_y[pp] + off;
 #pragma unroll
-                    for (int v = 0; v < VEC; ++v)
-                        if (fo[u] + v < p.f) st_peer_v1(q + v, acc[u][v]);
+                    for (int u = 0; u < U; ++u) {
+                        if (!o.act[u]) continue;
+                        float *q = base + o.fo[u];
+                        if (VEC == 4 && o.sv == 4 && o.fo[u] + 4 <= p.f_store) {
+                            st_peer_v4(q, o.acc[u]);
+                        } else if (VEC >= 2 && o.sv >= 2 && o.fo[u] + VEC <= p.f_store) {
+#pragma unroll
+                            for (int v = 0; v < VEC; v += 2) st_peer_v2(q + v, &o.acc[u][v]);
+                        } else {
+#pragma unroll
+                            for (int v = 0; v < VEC; ++v)
+                                if (o.fo[u] + v < p.f) st_peer_v1(q + v, o.acc[u][v]);
+                        }
+                    }
                 }
             }
         }
+        if (!bulk || p.n_peers <= 0 || (p.hints & 8)) continue;
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncwarp();
+        need_and = __reduce_and_sync(0xffffffffu, need_and);
+        const uint32_t all_peers = (p.n_peers >= 32) ? 0xffffffffu : ((1u << p.n_peers) - 1u);
+        const uint32_t tile_peers = whole ? (need_and & all_peers) : 0u;
+        if (lane == 0 && tile_peers) {
+            const uint32_t src = (uint32_t)__cvta_generic_to_shared(buf);
+            const uint32_t bytes = (uint32_t)RT * (uint32_t)stride * 4u;
+            const int64_t off = first_row * p.ldy;
+            for (int pp = 0; pp < p.n_peers; ++pp)
+                if ((tile_peers >> pp) & 1u)
+                    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+                                 :: "l"(p.peer_y[pp] + off), "r"(src), "r"(bytes) : "memory");
+        }
+        if (lane < RT && tile_peers != all_peers) {
+            const int32_t r = row_s[wic][lane];
+            if (r >= 0) {
+                uint32_t need = (p.peer_mask ? __ldg(p.peer_mask + r) : 0xffffffffu) & all_peers & ~tile_peers;
+                // the slab of this slot's task (a tile may straddle two slabs when it is not `whole`)
+                const int64_t task = t0 + lane;
+                const int f0 = whole ? f0_tile : (int)(task / per_slab) * SW;
+                int nfl = p.f - f0;
+                nfl = nfl > SW ? SW : nfl;
+                const uint32_t bytes = (uint32_t)((nfl + 3) & ~3) * 4u;       // pad columns lie inside ldy
+                const uint32_t src = (uint32_t)__cvta_generic_to_shared(buf + (size_t)lane * stride);
+                const int64_t off = (int64_t)r * p.ldy + f0;
+                for (int pp = 0; need; ++pp, need >>= 1)
+                    if (need & 1u)
+                        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+                                     :: "l"(p.peer_y[pp] + off), "r"(src), "r"(bytes) : "memory");
+            }
+        }
+        // every lane commits one (possibly empty) group per tile, so "1 pending" always means "the previous
+        // tile's stores"
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
     }
-    }  // if constexpr (PEERS)
-    }  // task loop
+    // completion (not just source reads): the peers' memory holds every row before this grid completes
+    if (p.hints & 64) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // measurement aid
+    else asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
 }
 
 template <int G, int VEC, int U, bool FUSED, int STD, bool PEERS, bool HOT>
 int32_t launch_hop(const HopDev &p, int64_t n_tasks, cudaStream_t s)
 {
     constexpr int GPW = 32 / G;
-    const int64_t warps = ceil_div(n_tasks, GPW * hop_tasks_per_warp(PEERS));
-    const int64_t blocks = ceil_div(warps, HOP_THREADS / 32);
-    if (blocks <= 0) return SGC_OK;
-    if (blocks > 0x7fffffffLL) {
-        set_error("spmm_hop: grid too large (%lld blocks)", (long long)blocks);
-        return SGC_ERR_INVALID;
+    if constexpr (PEERS) {
+        static_assert(STD == 0, "the peer variant has no fused standardisation");
+        const int RT = p.tpw * GPW;
+        const int64_t n_tiles = ceil_div(n_tasks, RT);
+        if (n_tiles <= 0) return SGC_OK;
+        const size_t smem = (size_t)(HOP_THREADS / 32) * 2 * RT * p.stage_stride * sizeof(float);
+        auto kern = spmm_hop_peers_kernel<G, VEC, U, FUSED, HOT>;
+        SGC_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        int occ = 0;
+        SGC_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, HOP_THREADS, smem));
+        if (occ < 1) {
+            set_error("spmm_hop: peer variant does not fit an SM (%zu bytes of shared memory)", smem);
+            return SGC_ERR_UNSUPPORTED;
+        }
+        const int64_t want = ceil_div(n_tiles, HOP_THREADS / 32);
+        const int64_t cap = (int64_t)sm_count() * occ;
+        kern<<<(unsigned)(want < cap ? want : cap), HOP_THREADS, smem, s>>>(p, n_tiles);
+        SGC_LAUNCH_CHECK();
+        return SGC_OK;
+    } else {
+        const int64_t warps = ceil_div(n_tasks, GPW);
+        const int64_t blocks = ceil_div(warps, HOP_THREADS / 32);
+        if (blocks <= 0) return SGC_OK;
+        if (blocks > 0x7fffffffLL) {
+            set_error("spmm_hop: grid too large (%lld blocks)", (long long)blocks);
+            return SGC_ERR_INVALID;
+        }
+        spmm_hop_kernel<G, VEC, U, FUSED, STD, HOT><<<(unsigned)blocks, HOP_THREADS, 0, s>>>(p);
+        SGC_LAUNCH_CHECK();
+        return SGC_OK;
     }
-    spmm_hop_kernel<G, VEC, U, FUSED, STD, PEERS, HOT><<<(unsigned)blocks, HOP_THREADS, 0, s>>>(p);
-    SGC_LAUNCH_CHECK();
-    return SGC_OK;
 }
 
 #endif  // __CUDACC__

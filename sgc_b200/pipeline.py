@@ -168,22 +168,24 @@ def host_threads():
 
 
 PCIE_BYTES_PER_US = 40e3        # ~40 GB/s: sustained pinned H2D rate of the strided / contiguous copies
-_scan_gave_up = False           # this host scans slower than PCIe uploads: stop trying (per process)
 
 
-def uniform_value(val_h, hidden_bytes=0):
+def uniform_value(val_h, hidden_bytes=0, report=None):
     """The common value when every stored value of the host CSR holds the same bits, else None.  The
     reference's adjacency matrices are constant-valued: 1.0 for the networkx adjacency of the citation
     graphs (utils.py:62), 2.0 for Reddit (`adj + adj.T` of a symmetric 0/1 matrix, utils.py:116); the
     device array is then filled in place of an nnz x 8-byte upload.  Exact -- a threaded bit compare over
     the whole array (sgc_host_all_equal_f64), run while the DMA engine is busy with the `hidden_bytes`
     enqueued ahead of it.  The scan gets the time those copies take plus the time the upload it replaces
-    would take; a host that cannot finish within that (it would lose time, not save it) gives up,
-    uploads, and does not try again in this process.  SGC_B200_UNIFORM_VALUES=0 switches the scan off,
-    =force removes the time budget."""
-    global _scan_gave_up
+    would take; a host that cannot finish within that (it would lose time, not save it) gives up and the
+    array is uploaded.  Nothing is remembered between calls: every call decides for itself, and a call
+    that gave up says so (`report["scan_gave_up"]`, surfaced in precompute_host's `stats`) so that a
+    caller on a slow host can pass detect_uniform_values=False.  SGC_B200_UNIFORM_VALUES=0 switches the
+    scan off, =force removes the time budget."""
+    if report is not None:
+        report["scan_gave_up"] = False
     mode = os.environ.get("SGC_B200_UNIFORM_VALUES", "1")
-    if mode == "0" or (_scan_gave_up and mode != "force"):
+    if mode == "0":
         return None
     if val_h.dtype != torch.float64 or not val_h.is_contiguous() or val_h.is_cuda or val_h.numel() == 0:
         return None
@@ -193,8 +195,8 @@ def uniform_value(val_h, hidden_bytes=0):
     nbytes = int(val_h.numel()) * 8
     budget_us = 0 if mode == "force" else max(500, int((hidden_bytes + nbytes) / PCIE_BYTES_PER_US))
     r = _ffi.lib().sgc_host_all_equal_f64(val_h.data_ptr(), int(val_h.numel()), first, host_threads(), budget_us)
-    if r == 2:
-        _scan_gave_up = True
+    if r == 2 and report is not None:
+        report["scan_gave_up"] = True
     return first if r == 1 else None
 
 
@@ -217,8 +219,9 @@ def precompute_host(adj, features, degree, standardize=False, out=None, out_bloc
               device array instead of uploading it (`uniform_value`; under `group` every rank scans its
               own 1/P and a one-word all-reduce makes the verdict common); default: on, except under
               `group`, where it measured neutral and is opt-in
-    stats     optional dict; receives h2d_bytes / d2h_bytes actually copied by this call and
-              uniform_value (the fill value, or None when the values were uploaded)
+    stats     optional dict; receives h2d_bytes / d2h_bytes actually copied by this call,
+              uniform_value (the fill value, or None when the values were uploaded) and scan_gave_up
+              (True when the host scan ran out of its time budget in THIS call; no state is kept)
     trace     optional list; receives (label, device ms since the start mark, host ms since the call) for
               the milestones of the schedule (CUDA events), for tools/e2e_sweep.py
     Returns `out` (complete when the call returns)."""
@@ -284,6 +287,7 @@ def precompute_host(adj, features, degree, standardize=False, out=None, out_bloc
             nbytes = lambda t: t.numel() * t.element_size()
             h2d = nbytes(rp_h) + nbytes(features)
             fill = None
+            scan_report = {"scan_gave_up": False}
             # under `group` the scan is opt-in: at N = 2 it measured neutral (16.3 vs 15.7 ms: the piece scan
             # and the verdict's read-back stall the enqueueing thread for as long as the upload they save)
             detect = (group is None) if detect_uniform_values is None else bool(detect_uniform_values)
@@ -311,7 +315,7 @@ def precompute_host(adj, features, degree, standardize=False, out=None, out_bloc
                     if by_cols:
                         upload_slab(*slabs[0])                 # keeps the DMA engine fed during the host scan
                         ahead += n * 4 * (slabs[0][1] - slabs[0][0])
-                    fill = uniform_value(val_h, ahead)
+                    fill = uniform_value(val_h, ahead, scan_report)
                     mark("values scanned", c_in)
                 if fill is not None:
                     val = torch.full((val_h.numel(),), fill, dtype=torch.float64, device=dev)
@@ -324,7 +328,8 @@ def precompute_host(adj, features, degree, standardize=False, out=None, out_bloc
             for c0, c1 in slabs[len(x_up):]:
                 upload_slab(c0, c1)
             if stats is not None:
-                stats.update(h2d_bytes=int(h2d), d2h_bytes=int(n * f * 4), uniform_value=fill)
+                stats.update(h2d_bytes=int(h2d), d2h_bytes=int(n * f * 4), uniform_value=fill,
+                             scan_gave_up=scan_report["scan_gave_up"])
         for t in (rp, col, val):
             t.record_stream(main)
         x.record_stream(c_in)

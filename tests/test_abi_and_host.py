@@ -57,7 +57,7 @@ def test_hop_args_layout_matches_c(built, tmp_path):
         "int main(void){printf(\"%zu\", sizeof(sgc_hop_args_t));\n"
         + "".join('printf(" %%zu", offsetof(sgc_hop_args_t, %s));\n' % f for f in
                   ["aval_d", "dinv_d", "dinv_rows_d", "sval_d", "x_d", "ldx", "y_d", "ldy", "partial_d", "ldp", "mean_d",
-                   "std_d", "f", "slab_floats", "flags", "hints", "n_peers", "reserved_", "peer_y_d", "peer_mask_d"])
+                   "std_d", "f", "slab_floats", "flags", "hints", "n_peers", "push_tile_tasks", "peer_y_d", "peer_mask_d"])
         + "return 0;}\n")
     exe = tmp_path / "layout"
     subprocess.check_call(["gcc", "-I", os.path.join(REPO, "include"), str(src), "-o", str(exe)])
@@ -252,12 +252,19 @@ def test_host_value_scan(built, monkeypatch):
     twos[77777] = 2.0
     monkeypatch.setenv("SGC_B200_UNIFORM_VALUES", "0")
     assert pipeline.uniform_value(twos) is None
-    # a host that cannot finish inside the budget gives up once and stops scanning in this process
+    # a host that cannot finish inside the budget gives up for THIS call only and says so; nothing is
+    # remembered between calls (no process-global state)
     monkeypatch.setenv("SGC_B200_UNIFORM_VALUES", "1")
-    monkeypatch.setattr(pipeline, "_scan_gave_up", True)
-    assert pipeline.uniform_value(twos) is None
-    monkeypatch.setattr(pipeline, "_scan_gave_up", False)
-    assert pipeline.uniform_value(twos, hidden_bytes=1 << 30) == 2.0
+    assert not hasattr(pipeline, "_scan_gave_up")
+    rep = {}
+    assert pipeline.uniform_value(twos, hidden_bytes=1 << 30, report=rep) == 2.0 and rep == {"scan_gave_up": False}
+    monkeypatch.setattr(pipeline, "PCIE_BYTES_PER_US", 1e12)          # a budget nobody can meet (500 us floor)
+    huge = torch.full((1 << 24,), 2.0, dtype=torch.float64)
+    monkeypatch.setenv("SGC_B200_HOST_THREADS", "1")
+    got = pipeline.uniform_value(huge, report=rep)
+    assert (got is None and rep["scan_gave_up"]) or (got == 2.0 and not rep["scan_gave_up"])
+    monkeypatch.setattr(pipeline, "PCIE_BYTES_PER_US", 40e3)
+    assert pipeline.uniform_value(twos, report=rep) == 2.0 and rep["scan_gave_up"] is False
 
 
 def test_textsgc_and_sparse_feature_entry_points_have_no_cpu_path():
@@ -272,25 +279,61 @@ def test_textsgc_and_sparse_feature_entry_points_have_no_cpu_path():
             fn(a)
 
 
-def test_bench_reference_arm_contract():
-    """`bench.py --impl reference` (the reference's CPU path on a bounded sample): exactly one JSON
-    line on stdout with the contract's keys; ranks other than 0 print nothing and exit 0."""
+def test_bench_reference_arm_contract(tmp_path):
+    """`bench.py --impl reference` (the staged, unmodified reference on the host cores): exactly one JSON
+    line on stdout with the contract's keys and the same `config` object the own arm prints; the process
+    imports nothing of the sgc_b200 package and maps no libsgc_b200.so; every step is a whole K-hop
+    utils.sgc_precompute; ranks other than 0 print nothing and exit 0."""
     import json
-    env = dict(os.environ, SGC_BENCH_CPU_FRACTION="64", CUDA_VISIBLE_DEVICES="")
-    cmd = [sys.executable, os.path.join(REPO, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0"]
-    r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
+    env = dict(os.environ, SGC_BENCH_SCALE="0.02")
+    env.pop("CUDA_VISIBLE_DEVICES", None)
+    probe = tmp_path / "probe.txt"
+    wrapper = ("import runpy, sys\n"
+               "sys.argv = ['bench.py'] + sys.argv[1:]\n"
+               "try:\n"
+               "    runpy.run_path(%r, run_name='__main__')\n"
+               "finally:\n"
+               "    mods = sorted(m for m in sys.modules if m.split('.')[0] in ('sgc_b200', 'oracle'))\n"
+               "    maps = [l for l in open('/proc/self/maps') if 'libsgc_b200' in l or 'liboracle' in l]\n"
+               "    import torch\n"
+               "    open(%r, 'w').write(repr((mods, len(maps), torch.cuda.is_initialized())))\n"
+               % (os.path.join(REPO, "bench.py"), str(probe)))
+    cmd = [sys.executable, "-c", wrapper, "--impl", "reference", "--steps", "2", "--warmup", "1"]
+    r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600, cwd=REPO)
     assert r.returncode == 0, r.stderr[-2000:]
     lines = [l for l in r.stdout.splitlines() if l.strip()]
     assert len(lines) == 1, lines
     d = json.loads(lines[0])
     assert d["impl"] == "reference" and d["value"] > 0 and d["unit"] == "edge*feat/s" and d["higher_is_better"] is True
-    assert d["steps"] == 1 and d["warmup"] == 0 and d["n_gpus"] == 1 and d["gpu_launches"] == 0
+    assert d["steps"] == 2 and d["warmup"] == 1 and d["n_gpus"] == 1 and d["gpu_launches"] == 0
     assert d["config"]["workload"].startswith("Reddit-shaped") and "model" not in d["config"]
-    assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] >= 1 and d["cpu_baseline"]["sample"]
+    staged = os.path.exists(os.path.join(REPO, "baseline", "_ref", "utils.py"))
+    assert d["cpu_baseline"]["kind"] == ("reference" if staged else "port")
+    assert d["cpu_baseline"]["cores"] >= 1 and "utils.sgc_precompute" in d["cpu_baseline"]["sample"]
     assert d["cpu_baseline"]["value"] == d["value"] == d["e2e"]["value"]
     assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["d2h_bytes_per_step"] == 0
-    r = subprocess.run(cmd + ["--gpus", "2"], env=dict(env, RANK="1", WORLD_SIZE="2", LOCAL_RANK="1"),
-                       capture_output=True, text=True, timeout=600)
+    assert d["details"]["steps_requested"] == 2 and len(d["details"]["step_ms"]) == 2
+    # `config` is a pure function of the workload: the own arm prints the identical object
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("_bench_for_test", os.path.join(REPO, "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    c = d["config"]
+    assert bench.workload_config("reddit", c["nodes"], c["nnz_S"], c["features"], c["k_hops"]) == c
+    mods, n_maps, cuda_init = eval(probe.read_text())
+    assert n_maps == 0 and not cuda_init, (mods, n_maps, cuda_init)
+    assert not [m for m in mods if m.startswith("sgc_b200")], mods
+    if staged:
+        assert mods == [], mods                       # not even the oracle port
+    # a time budget that does not hold the requested steps: fewer WHOLE steps, and the line says so
+    r = subprocess.run([sys.executable, os.path.join(REPO, "bench.py"), "--impl", "reference", "--steps", "5",
+                        "--warmup", "3"], env=dict(env, SGC_BENCH_REF_BUDGET_S="0.001"), capture_output=True, text=True,
+                       timeout=600)
+    d = json.loads(r.stdout.strip())
+    assert d["steps"] == 1 and d["warmup"] == 1 and d["details"]["steps_requested"] == 5
+    assert "whole workload" in d["cpu_baseline"]["sample"] and "1 whole steps timed (5 requested" in d["cpu_baseline"]["sample"]
+    r = subprocess.run([sys.executable, os.path.join(REPO, "bench.py"), "--impl", "reference", "--gpus", "2"],
+                       env=dict(env, RANK="1", WORLD_SIZE="2", LOCAL_RANK="1"), capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and r.stdout.strip() == ""
 
 
