@@ -412,8 +412,8 @@ def run_own(args):
         sys.stdout = os.fdopen(saved, "w")
         dist.init_process_group("nccl", device_id=dev)
     if world > 1:
-        from sgc_b200 import dist as sgc_dist
-        return sgc_dist.bench(args, rank, world, dev, globals())
+        import bench_dist
+        return bench_dist.bench(args, rank, world, dev, globals())
 
     synth = load_synth()
     name = args.workload

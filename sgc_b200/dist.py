@@ -95,7 +95,8 @@ def default_mode(device):
 
 def _cuda_hop(graph, x, out, peers=None, peer_mask=None):
     from .propagate import hop
-    hop(graph, x, out=out, peers=peers, peer_mask=peer_mask)
+    # `out` is always a row range of a full-height padded operand (ld = pad_ld(f), pad columns zero)
+    hop(graph, x, out=out, peers=peers, peer_mask=peer_mask, pad_owned=True)
 
 
 def halo_enabled():
@@ -139,7 +140,12 @@ class _DeviceMemory(object):
                                          "version": 2, "strides": None}
 
 
-def _release_symm(local_ptr, peer_ptrs):
+def _release_symm(local_ptr, peer_ptrs, state):
+    """Finaliser of last resort (interpreter exit / a rank that died): unmaps and frees without a rendezvous.
+    The orderly path is SymmetricBuffer.close()."""
+    if state["closed"]:
+        return
+    state["closed"] = True
     lib = _ffi.lib()
     for ptr in peer_ptrs:
         lib.sgc_ipc_close(ptr)
@@ -176,7 +182,8 @@ class SymmetricBuffer(object):
                 opened.append(int(peer.value))
             self.tensor = torch.as_tensor(_DeviceMemory(ptr.value, (self.rows, self.ld)), device=device)
         dist.barrier(group=group)          # nobody frees or writes before everyone has mapped
-        self._fin = weakref.finalize(self, _release_symm, int(ptr.value), opened)
+        self._local, self._opened, self._state = int(ptr.value), opened, {"closed": False}
+        self._fin = weakref.finalize(self, _release_symm, self._local, opened, self._state)
 
     def row_ptrs(self, row, peers_only):
         """Device address of row `row` in every rank's copy (optionally without this rank's)."""
@@ -184,8 +191,19 @@ class SymmetricBuffer(object):
         return [p + off for r, p in enumerate(self.ptrs) if not (peers_only and r == self.rank)]
 
     def close(self):
+        """Collective: every rank unmaps its peers' buffers, the ranks meet, and only then is the local
+        allocation freed -- cudaFree of exported memory while another process still has it mapped
+        (cudaIpcOpenMemHandle without the matching close) is undefined behaviour."""
+        if self._state["closed"]:
+            return
         self.tensor = None
-        self._fin()
+        self._state["closed"] = True
+        lib = _ffi.lib()
+        torch.cuda.synchronize()
+        for ptr in self._opened:
+            lib.sgc_ipc_close(ptr)
+        dist.barrier(group=self.group)
+        lib.sgc_symm_free(self._local)
 
 
 class ShardedPropagator(object):
@@ -266,19 +284,24 @@ class ShardedPropagator(object):
                       self.ld, torch.cuda.current_stream().cuda_stream)
         self._barrier()
 
-    def _push_propagate(self, degree):
+    def _push_hop(self, k, degree):
+        """Hop k of `degree` in push mode: gathers from buf[k % 2], writes this rank's rows into its own
+        segment of buf[(k+1) % 2] and (unless it is the last hop) into every peer's, then the barrier."""
         sg = self.sg
+        src, dst = self.buf[k % 2], self.symm[(k + 1) % 2]
+        last = (k == degree - 1)
+        if sg.n_local > 0:
+            peers = None if (last or sg.world == 1) else dst.row_ptrs(sg.row0, peers_only=True)
+            self.hop_fn(sg.graph, src[:, :self.f], dst.tensor[sg.row0:sg.row1, :self.f], peers,
+                        None if peers is None else self.peer_mask)
+        # after the barrier: all rows of hop k are in place everywhere, and nobody still reads
+        # the buffer the next hop (or the next load) overwrites
+        self._barrier()
+
+    def _push_propagate(self, degree):
         for k in range(degree):
-            src, dst = self.buf[k % 2], self.symm[(k + 1) % 2]
-            last = (k == degree - 1)
-            if sg.n_local > 0:
-                peers = None if (last or sg.world == 1) else dst.row_ptrs(sg.row0, peers_only=True)
-                self.hop_fn(sg.graph, src[:, :self.f], dst.tensor[sg.row0:sg.row1, :self.f], peers,
-                            None if peers is None else self.peer_mask)
-            # after the barrier: all rows of hop k are in place everywhere, and nobody still reads
-            # the buffer the next hop (or the next load) overwrites
-            self._barrier()
-        return self.buf[degree % 2][sg.row0:sg.row1, :self.f]
+            self._push_hop(k, degree)
+        return self.buf[degree % 2][self.sg.row0:self.sg.row1, :self.f]
 
     # -- exchange mode ---------------------------------------------------------------------------
     def _exchange_block(self, dst, r):
@@ -369,6 +392,150 @@ def propagate_sharded(sg, x_local, degree, row_blocks=None, group=None, hop_fn=N
 
 
 # --------------------------------------------------------------------------------------------------
+# Result checks of the multi-GPU paths (bench.py --gpus N runs them after the timed steps and fails on a
+# mismatch; tests/test_gpu_dist.py drives them too).  The contract is the reference's: "same numbers as one
+# process" (utils.py:92-97 has no notion of ranks) -- here bit for bit.
+def block_checksum(t, row0, col0, f_total, chunk_elems=1 << 23):
+    """Position-sensitive 64-bit checksum of the BITS of an fp32 block [r, c] whose element (i, j) is element
+    (row0 + i, col0 + j) of a logical [*, f_total] matrix: sum over elements of bits * (hash(global index) | 1)
+    in wrap-around int64.  Two ranks (or one GPU and many) hold the same numbers iff the sums agree, whatever
+    the partition.  Device-side, no host copy."""
+    from . import synth
+    r, c = int(t.shape[0]), int(t.shape[1])
+    dev = t.device
+    total = torch.zeros((), dtype=torch.int64, device=dev)
+    if r == 0 or c == 0:
+        return total
+    rows_per = max(1, chunk_elems // c)
+    cols = torch.arange(c, dtype=torch.int64, device=dev) + int(col0)
+    for a in range(0, r, rows_per):
+        b = min(a + rows_per, r)
+        bits = t[a:b].contiguous().view(torch.int32).to(torch.int64) & 0xFFFFFFFF
+        idx = (torch.arange(a, b, dtype=torch.int64, device=dev) + int(row0))[:, None] * int(f_total) + cols[None, :]
+        total = total + (bits * (synth.mix64(idx) | 1)).sum()
+    return total
+
+
+def verify_against_single(y_local, y_single, row0, col0, f_total, group=None):
+    """Collective.  Every rank's output block [rows row0.., columns col0..] against the same block of the
+    single-GPU result `y_single` (held by rank 0 only; None elsewhere), by block_checksum.  Returns
+    {"ok", "per_rank", "checksum"} on every rank."""
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    dev = y_local.device
+    r, c = int(y_local.shape[0]), int(y_local.shape[1])
+    mine = torch.stack([torch.tensor(v, dtype=torch.int64, device=dev) for v in (row0, r, col0, c)]
+                       + [block_checksum(y_local, row0, col0, f_total)])
+    allv = torch.empty(world * 5, dtype=torch.int64, device=dev)
+    dist.all_gather_into_tensor(allv, mine, group=group)
+    allv = allv.view(world, 5).cpu().tolist()
+    ok = torch.ones(world, dtype=torch.int64, device=dev)
+    if rank == 0:
+        for q, (r0, rr, c0, cc, got) in enumerate(allv):
+            want = int(block_checksum(y_single[r0:r0 + rr, c0:c0 + cc], r0, c0, f_total).item())
+            ok[q] = 1 if want == got else 0
+    dist.broadcast(ok, 0, group=group)
+    per_rank = [bool(v) for v in ok.cpu().tolist()]
+    total = 0
+    for row in allv:
+        total = (total + row[4]) & 0xFFFFFFFFFFFFFFFF
+    return {"ok": all(per_rank), "per_rank": per_rank, "checksum": "%016x" % total,
+            "what": "every rank's output block vs the same block of the single-GPU result (rank 0), bit-level "
+                    "position-sensitive 64-bit checksum of all %d elements" % sum(row[1] * row[3] for row in allv)}
+
+
+def _bits_differ(a, b):
+    return (a.contiguous().view(torch.int32) != b.contiguous().view(torch.int32)).any(dim=1)
+
+
+def _replication_mismatches(prop, buf, masked, rows_per_rank, group):
+    """Collective.  Sampled rows of every rank's segment of the full-height operand `buf`: the owner's own
+    copy is the truth (all-gathered), every other rank compares its copy bit for bit -- only where its shard
+    gathers that row when `masked` (halo masks: other rows are never pushed to it).  Returns the global
+    number of differing (row, rank) pairs and of compared pairs."""
+    sg = prop.sg
+    dev = buf.device
+    m = max(1, min(int(rows_per_rank), min(b - a for a, b in prop.parts)))
+    gens = []
+    for q in range(sg.world):
+        g = torch.Generator(device="cpu")
+        g.manual_seed(1000 + q)
+        nq = prop.parts[q][1] - prop.parts[q][0]
+        gens.append(torch.sort(torch.randperm(nq, generator=g)[:m])[0].to(dev) + q * sg.n_pad)
+    truth = torch.empty((sg.world * m, buf.shape[1]), dtype=torch.float32, device=dev)
+    _all_gather(truth, buf[gens[sg.rank]].contiguous(), group, False)
+    touch = None
+    if masked:
+        touch = torch.zeros(sg.world * sg.n_pad, dtype=torch.bool, device=dev)
+        if sg.graph.nnz:
+            touch[sg.graph.col.long()] = True
+    bad = torch.zeros(2, dtype=torch.int64, device=dev)
+    for q in range(sg.world):
+        if q == sg.rank:
+            continue
+        diff = _bits_differ(buf[gens[q]], truth[q * m:(q + 1) * m])
+        need = touch[gens[q]] if masked else torch.ones_like(diff)
+        bad[0] += (diff & need).sum()
+        bad[1] += need.sum()
+    dist.all_reduce(bad, group=group)
+    return int(bad[0].item()), int(bad[1].item())
+
+
+def verify_sharded(prop, x_local, degree, B, y_single=None, rows_per_rank=256, group=None):
+    """Collective check of the row-sharded (push) propagation, hop by hop, on the live buffers:
+      * after the load and after every exchanging hop: sampled rows of every rank's segment are bit-identical
+        on the owner and on every rank that gathers them (the NVLink pushes landed, complete and in place);
+      * every hop: sampled output rows of this rank recomputed by the reference's torch.spmm on the CPU from
+        this rank's full-height operand (B["sampled_rows_check"]), north_star tolerance;
+      * with y_single (rank 0's single-GPU result of the same workload): every rank's final rows against it,
+        bit for bit (block_checksum).
+    B: bench.py's globals (the CPU checker lives there, not in this package).  Returns the report (same on
+    every rank); "ok" False on any mismatch."""
+    sg, f = prop.sg, prop.f
+    dev = sg.graph.device
+    assert prop.mode == "push", "verify_sharded drives the fused (push) path"
+    ref = B["Reference"]()
+    rep = {"hops": [], "rows_per_rank": rows_per_rank}
+    prop.load(x_local)
+    torch.cuda.synchronize(dev)
+    bad, cmp_ = _replication_mismatches(prop, prop.buf[0], False, rows_per_rank, group)
+    rep["load"] = {"replicated_rows_compared": cmp_, "mismatches": bad}
+    ok = bad == 0
+    rows = B["sample_rows"](sg.n_local, rows_per_rank, dev, seed=11 + sg.rank) if sg.n_local else None
+    for k in range(degree):
+        prop._push_hop(k, degree)
+        torch.cuda.synchronize(dev)
+        src, out = prop.buf[k % 2][:, :f], prop.buf[(k + 1) % 2][sg.row0:sg.row1, :f]
+        viol = torch.zeros(3, dtype=torch.int64, device=dev)
+        maxd = torch.zeros(1, dtype=torch.float64, device=dev)
+        if rows is not None:
+            r = B["sampled_rows_check"](ref, sg.graph, src, out, rows)
+            viol += torch.tensor([r["violations"], r["elements"], r["bit_identical_elements"]], device=dev)
+            maxd[0] = r["max_abs_diff"]
+        dist.all_reduce(viol, group=group)
+        dist.all_reduce(maxd, op=dist.ReduceOp.MAX, group=group)
+        hop_rep = {"hop": k + 1, "vs_reference_spmm": {"elements": int(viol[1]), "violations": int(viol[0]),
+                                                       "bit_identical_elements": int(viol[2]),
+                                                       "max_abs_diff": float(maxd[0])}}
+        ok = ok and int(viol[0]) == 0
+        if k < degree - 1 and sg.world > 1:
+            bad, cmp_ = _replication_mismatches(prop, prop.buf[(k + 1) % 2], prop.peer_mask is not None,
+                                                rows_per_rank, group)
+            hop_rep["pushed_rows"] = {"compared": cmp_, "mismatches": bad}
+            ok = ok and bad == 0
+        rep["hops"].append(hop_rep)
+    y_local = prop.buf[degree % 2][sg.row0:sg.row1, :f]
+    single_flag = torch.tensor([1 if y_single is not None else 0], dtype=torch.int64, device=dev)
+    dist.all_reduce(single_flag, group=group)
+    if int(single_flag.item()) > 0:
+        rep["vs_single_gpu"] = verify_against_single(y_local, y_single, sg.row0, 0, f, group)
+        ok = ok and rep["vs_single_gpu"]["ok"]
+    rep["ok"] = bool(ok)
+    rep["checker"] = ("the reference's torch.spmm on CPU (%s) on %d sampled rows per rank and hop; owner-vs-copy "
+                      "bit compare of sampled pushed rows; tolerance %s" % (ref.kind, rows_per_rank, B["TOLERANCE"]))
+    return rep
+
+
+# --------------------------------------------------------------------------------------------------
 def local_rows_of(graph_csr, row0, row1):
     """Slice [row0, row1) of a CSR given as (row_ptr, col, val) tensors."""
     row_ptr, col, val = graph_csr
@@ -414,345 +581,3 @@ def propagate_feature_sharded(graph, x_cols, degree, **kw):
     the same columns of S^K X, bit-identical to those columns of the single-GPU result."""
     from .propagate import propagate
     return propagate(graph, x_cols, degree, **kw)
-
-
-def run_feature_sharded_workload(name, args, rank, world, dev, B, with_e2e=True, want_single=True):
-    """bench leg for sharding == 'features' (see run_sharded_workload for the contract)."""
-    from . import _ffi, synth
-    from .features import col_stats, standardize_, to_padded
-    from .graph import normalize_csr
-    from .propagate import default_chunk, propagate
-    shape = synth.SHAPES[name]
-    n, f, k = shape["n"], shape["f"], shape["k"]
-    c0, c1 = partition_features(f, world)[rank]
-    s = synth.make_shape(name, device=dev, with_features=False, lam=bench_lambda())
-    x = synth.gaussian_features(n, f, seed=1, scaled=shape["scaled"], device=dev)
-    x_raw_local = x[:, c0:c1].contiguous()
-    if shape["scaled"]:
-        mean, std = col_stats(x)
-        standardize_(x, mean, std)
-    torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    graph = normalize_csr(n, s["row_ptr"], s["col"], s["val"])
-    torch.cuda.synchronize()
-    normalise_ms = (time.perf_counter() - t0) * 1e3
-    single = None
-    if rank == 0 and want_single:
-        xp = to_padded(x)
-        for _ in range(3):
-            propagate(graph, xp, k)
-        torch.cuda.synchronize()
-        ms1 = _device_ms(lambda: propagate(graph, xp, k), 5)
-        single = {"n_gpus": 1, "ms_per_step": ms1, "value": k * graph.nnz * f / (ms1 * 1e-3)}
-        del xp
-    x_local = to_padded(x[:, c0:c1]) if c1 > c0 else None
-    del x
-    torch.cuda.empty_cache()
-    nnz = graph.nnz
-    graph.plan(default_chunk())
-
-    def step():
-        return propagate(graph, x_local, k) if x_local is not None else None
-
-    for _ in range(args.warmup):
-        step()
-    torch.cuda.synchronize()
-    dist.barrier()
-    sampler = B["ClockSampler"](dev.index)
-    sampler.start()
-    launches0 = _ffi.launch_count()
-    torch.cuda.synchronize()
-    dist.barrier()
-    start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    start.record()
-    for _ in range(args.steps):
-        step()
-    stop.record()
-    torch.cuda.synchronize()
-    dist.barrier()
-    ms = torch.tensor([start.elapsed_time(stop)], dtype=torch.float64, device=dev)
-    dist.all_reduce(ms, op=dist.ReduceOp.MAX)            # max over ranks, device-timed
-    launches = _ffi.launch_count() - launches0
-    clocks = sampler.stop()
-    ms_per_step = float(ms.item()) / args.steps
-    out = {"name": name, "n": n, "f": f, "k": k, "nnz": nnz, "n_pad": n, "mode": "features",
-           "push_fraction": 0.0, "n_blocks": 1, "normalise_ms": normalise_ms, "ms_per_step": ms_per_step,
-           "value": k * nnz * f / (ms_per_step * 1e-3), "launches": int(launches), "clocks": clocks,
-           "single": single, "e2e": None, "cols_per_rank": max(b - a for a, b in partition_features(f, world))}
-    if with_e2e and x_local is not None:
-        host = {kk: s[kk].cpu().pin_memory() for kk in ("row_ptr", "col", "val")}
-        host["x"] = x_raw_local.cpu().pin_memory()
-        out_host = torch.empty((n, c1 - c0), dtype=torch.float32).pin_memory()
-
-        from .pipeline import precompute_host
-        host_csr = (n, host["row_ptr"], host["col"], host["val"])
-        # one node, one copy of the adjacency in host memory: every rank uploads 1/P of it and NVLink
-        # replicates it (SGC_B200_SHARED_CSR=0: every rank uploads all of it)
-        shared_csr = os.environ.get("SGC_B200_SHARED_CSR", "1") != "0" and \
-            all(b > a for a, b in partition_features(f, world))       # the all-gather needs every rank
-
-        st = {}
-
-        def e2e_step():
-            # this rank's column block through the pipelined host-to-host path (pipeline.py): CSR up,
-            # K1/K2 under the upload of X, per slab K3 + hops + strided D2H
-            precompute_host(host_csr, host["x"], k, standardize=bool(shape["scaled"]), out=out_host,
-                            group=dist.group.WORLD if shared_csr else None, stats=st)
-
-        e2e_step()
-        dist.barrier()
-        e2e_steps = max(2, min(args.steps, 3))
-        t0 = time.perf_counter()
-        for _ in range(e2e_steps):
-            e2e_step()
-        dist.barrier()
-        e2e_s = torch.tensor([(time.perf_counter() - t0) / e2e_steps], dtype=torch.float64, device=dev)
-        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
-        # bytes this rank actually copied (col / val: 1/P per rank when shared, the rest over NVLink; a
-        # constant value array is filled on the GPU, not uploaded), summed over ranks
-        h2d = torch.tensor([st["h2d_bytes"]], dtype=torch.int64, device=dev)
-        dist.all_reduce(h2d)
-        out["e2e"] = {"value": k * nnz * f / float(e2e_s.item()), "unit": B["UNIT"],
-                      "h2d_bytes_per_step": int(h2d.item()), "d2h_bytes_per_step": int(n * f * 4),
-                      "ms_per_step": float(e2e_s.item()) * 1e3,
-                      "path": "per rank: sgc_b200.precompute_host on its column block (pipeline.py); adjacency "
-                              + ("uploaded once per node (1/P per rank over its own PCIe link, NCCL all-gather "
-                                 "over NVLink)" if shared_csr else "uploaded by every rank")
-                              + ("" if st.get("uniform_value") is None else
-                                 "; its stored values are all %g (exact host scan every step, 1/P per rank + "
-                                 "one-word all-reduce): filled on the GPU instead of uploaded" % st["uniform_value"])}
-    elif with_e2e:
-        dist.barrier(); dist.barrier()
-        z = torch.zeros(1, dtype=torch.float64, device=dev); dist.all_reduce(z, op=dist.ReduceOp.MAX)
-        z = torch.zeros(1, dtype=torch.int64, device=dev); dist.all_reduce(z)
-    del graph, x_local, s
-    torch.cuda.empty_cache()
-    return out
-
-
-def _device_ms(fn, reps):
-    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    a.record()
-    for _ in range(reps):
-        fn()
-    b.record()
-    torch.cuda.synchronize()
-    return a.elapsed_time(b) / reps
-
-
-def _single_gpu_reference(s, x, n, f, k, dev):
-    """K hops of the whole graph on one GPU (rank 0), device-timed; for the strong-scaling ratio."""
-    from .graph import normalize_csr
-    from .propagate import propagate
-    from .features import to_padded
-    g = normalize_csr(n, s["row_ptr"], s["col"], s["val"])
-    xp = to_padded(x)
-    for _ in range(3):
-        propagate(g, xp, k)
-    torch.cuda.synchronize()
-    ms = _device_ms(lambda: propagate(g, xp, k), 5)
-    out = {"n_gpus": 1, "ms_per_step": ms, "value": k * g.nnz * f / (ms * 1e-3)}
-    del g, xp
-    torch.cuda.empty_cache()
-    return out
-
-
-def bench_lambda():
-    """SGC_BENCH_LAMBDA: fraction of sampled edges forced into the source's own 1/8 block of nodes
-    (synth.powerlaw_graph `lam`; 0 = uniformly random neighbours, the default)."""
-    return float(os.environ.get("SGC_BENCH_LAMBDA", "0"))
-
-
-def _workload_inputs(name, rank, world, dev, want_single):
-    """This rank's rows of the named synthetic workload: raw CSR slice (global column ids) and the
-    feature rows the hops start from (Reddit shape: standardised as utils.py:119 does, with the
-    statistics of ALL rows).  Rank 0 also times the whole workload on its one GPU."""
-    from . import synth
-    from .features import col_stats, standardize_
-    shape = synth.SHAPES[name]
-    n, f, k = shape["n"], shape["f"], shape["k"]
-    n_pad, parts = partition_rows(n, world)
-    row0, row1 = parts[rank]
-    lam = bench_lambda()
-    single = None
-    if shape["symmetric"]:
-        s = synth.make_shape(name, device=dev, with_features=False, lam=lam)     # every rank builds the graph, keeps its rows
-        rp, col, val = local_rows_of((s["row_ptr"], s["col"], s["val"]), row0, row1)
-        if shape["scaled"]:
-            x = synth.gaussian_features(n, f, seed=1, scaled=True, device=dev)
-            mean, std = col_stats(x)
-            standardize_(x, mean, std)
-            x_local = x[row0:row1].clone()
-        else:
-            x = None
-            x_local = synth.gaussian_features(n, f, seed=1, scaled=False, row_range=(row0, row1), device=dev)
-        if rank == 0 and want_single:
-            if x is None:
-                x = synth.gaussian_features(n, f, seed=1, scaled=False, device=dev)
-            single = _single_gpu_reference(s, x, n, f, k, dev)
-        del s, x
-    else:
-        s = synth.make_shape(name, device=dev, with_features=False, row_range=(row0, row1), lam=lam)
-        rp, col, val = s["row_ptr"], s["col"], s["val"]
-        x_local = synth.gaussian_features(n, f, seed=1, scaled=False, row_range=(row0, row1), device=dev)
-        del s
-    torch.cuda.empty_cache()
-    return n, f, k, n_pad, rp, col, val, x_local, single
-
-
-def run_sharded_workload(name, args, rank, world, dev, B, with_e2e=True, want_single=True):
-    """Times K-hop sharded propagation of one named workload on `world` GPUs (strong scaling: the
-    graph is fixed; rows or feature columns are split over the ranks, see choose_sharding).
-    Returns the measurements on rank 0."""
-    from . import _ffi, synth
-    from .propagate import default_chunk
-    shape = synth.SHAPES[name]
-    approx_nnz = shape["pairs"] * (2 if shape["symmetric"] else 1) + shape["n"]
-    if choose_sharding(shape["n"], approx_nnz, shape["f"], world) == "features":
-        return run_feature_sharded_workload(name, args, rank, world, dev, B, with_e2e, want_single)
-    n, f, k, n_pad, rp, col, val, x_local, single = _workload_inputs(name, rank, world, dev, want_single)
-    torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    sg = shard_normalize(n, rp, col, val)
-    torch.cuda.synchronize()
-    normalise_ms = (time.perf_counter() - t0) * 1e3
-    nnz_local = torch.tensor([sg.graph.nnz], dtype=torch.int64, device=dev)
-    dist.all_reduce(nnz_local)
-    nnz = int(nnz_local.item())
-    prop = ShardedPropagator(sg, f)
-    mode = prop.mode
-    for blk in prop.blocks:
-        if blk is not None:
-            blk.plan(default_chunk())
-
-    for _ in range(args.warmup):
-        prop.load(x_local)
-        prop.propagate_resident(k)
-    torch.cuda.synchronize()
-    dist.barrier()
-    sampler = B["ClockSampler"](dev.index)
-    sampler.start()
-    launches0 = _ffi.launch_count()
-    total = 0.0
-    for _ in range(args.steps):
-        prop.load(x_local)         # untimed: X resident on every rank, the reference's starting state
-        torch.cuda.synchronize()
-        dist.barrier()
-        start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        start.record()
-        prop.propagate_resident(k)
-        stop.record()
-        torch.cuda.synchronize()
-        total += start.elapsed_time(stop)
-    dist.barrier()
-    ms = torch.tensor([total], dtype=torch.float64, device=dev)
-    dist.all_reduce(ms, op=dist.ReduceOp.MAX)            # max over ranks, device-timed
-    launches = _ffi.launch_count() - launches0
-    clocks = sampler.stop()
-    ms_per_step = float(ms.item()) / args.steps
-    out = {"name": name, "n": n, "f": f, "k": k, "nnz": nnz, "n_pad": n_pad, "mode": mode,
-           "push_fraction": getattr(prop, "push_fraction", 1.0),
-           "n_blocks": prop.n_blocks, "normalise_ms": normalise_ms, "ms_per_step": ms_per_step,
-           "value": k * nnz * f / (ms_per_step * 1e-3), "launches": int(launches), "clocks": clocks,
-           "single": single, "e2e": None}
-    if with_e2e:
-        # end to end: this rank's shard from pinned host memory and back
-        host = {"rp": rp.cpu().pin_memory(), "col": col.cpu().pin_memory(), "val": val.cpu().pin_memory(),
-                "x": x_local.cpu().pin_memory()}
-        out_host = torch.empty((sg.n_local, f), dtype=torch.float32).pin_memory()
-
-        def e2e_step():
-            sgl = shard_normalize(n, host["rp"].to(dev, non_blocking=True), host["col"].to(dev, non_blocking=True),
-                                  host["val"].to(dev, non_blocking=True))
-            xl = host["x"].to(dev, non_blocking=True)
-            if mode == "push":
-                yl = prop.rebind(sgl).propagate(xl, k)      # symmetric buffers + peer mappings are reused
-            else:
-                yl = ShardedPropagator(sgl, f).propagate(xl, k)
-            out_host.copy_(yl, non_blocking=True)
-            torch.cuda.synchronize()
-
-        e2e_step()
-        dist.barrier()
-        e2e_steps = max(2, min(args.steps, 3))
-        t0 = time.perf_counter()
-        for _ in range(e2e_steps):
-            e2e_step()
-        dist.barrier()
-        e2e_s = torch.tensor([(time.perf_counter() - t0) / e2e_steps], dtype=torch.float64, device=dev)
-        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
-        h2d = torch.tensor([sum(t.numel() * t.element_size() for t in host.values())], dtype=torch.int64, device=dev)
-        dist.all_reduce(h2d)
-        out["e2e"] = {"value": k * nnz * f / float(e2e_s.item()), "unit": B["UNIT"],
-                      "h2d_bytes_per_step": int(h2d.item()), "d2h_bytes_per_step": int(n * f * 4),
-                      "ms_per_step": float(e2e_s.item()) * 1e3}
-        del host, out_host
-    prop.close()
-    del prop, sg
-    torch.cuda.empty_cache()
-    return out
-
-
-def _parallelism_text(r, world):
-    if r["mode"] == "features":
-        return ("feature-sharded x%d: S replicated on every GPU, X split into contiguous column blocks of <= %d "
-                "columns; column c of S^K X depends on column c of X only, so the K hops (and the per-column "
-                "standardisation) need no exchange; output column-sharded" % (world, r.get("cols_per_rank", 0)))
-    if r["mode"] == "push":
-        return ("row-sharded x%d; exchange fused into the SpMM kernel: every output row is staged in shared memory "
-                "and written by cp.async.bulk to all peers' next-hop operands over NVLink (CUDA-IPC mapped), one "
-                "1-element all-reduce as barrier per hop; a row goes only to the peers whose shard gathers it "
-                "(%.1f%% of rows x peers here); X replicated at start, output sharded"
-                % (world, 100.0 * r["push_fraction"]))
-    return ("row-sharded x%d; per-hop NVLink exchange (NCCL send/recv groups) pipelined with the SpMM over %d row "
-            "blocks; X replicated at start, output sharded" % (world, r["n_blocks"]))
-
-
-def bench(args, rank, world, dev, B):
-    """bench.py --gpus N (N > 1): the SAME workload as N = 1 (Reddit-shaped, BASELINE configs[2]) row-sharded
-    over the N GPUs, so that value(N) / value(1) is a strong-scaling ratio; by default the line also
-    carries the products-shaped workload (BASELINE configs[3], the config north_star names for the
-    1/2/4/8-GPU series) with its own single-GPU reference (SGC_BENCH_EXTRA="" to skip).
-    B: bench.py's module globals (helpers)."""
-    import json
-    name = args.workload
-    r = run_sharded_workload(name, args, rank, world, dev, B,
-                             with_e2e=(name != "papers100m" or os.environ.get("SGC_BENCH_PAPERS_E2E") == "1"))
-    extras = {}
-    extra_names = os.environ.get("SGC_BENCH_EXTRA", "products" if not args.workload_given else "")
-    for other in [e for e in extra_names.split(",") if e and e != name]:
-        try:
-            x = run_sharded_workload(other, args, rank, world, dev, B, with_e2e=False)
-            extras[other] = {"workload": B["workload_config"](other, x["n"], x["nnz"], x["f"], x["k"])["workload"],
-                             "n_gpus": world, "value": x["value"], "unit": B["UNIT"], "ms_per_step": x["ms_per_step"],
-                             "nnz_S": x["nnz"], "dist_mode": x["mode"], "single_gpu_same_workload": x["single"],
-                             "strong_scaling_efficiency": (x["value"] / (world * x["single"]["value"])
-                                                           if x["single"] else None)}
-        except Exception as exc:            # an optional extra must never cost the primary line
-            extras[other] = {"error": repr(exc)[:300]}
-    if rank == 0:
-        n, f, k, nnz = r["n"], r["f"], r["k"], r["nnz"]
-        peak, peak_src = B["peaks"]()
-        b_hop = B["hop_bytes"](n, nnz, f)
-        achieved = k * b_hop / world / (r["ms_per_step"] * 1e-3) / 1e9      # per-GPU algorithmic GB/s
-        line = {
-            "metric": B["METRIC"], "value": r["value"], "unit": B["UNIT"], "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "strong",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": B["workload_config"](name, n, nnz, f, k, parallelism=_parallelism_text(r, world),
-                                           dist_mode=r["mode"], normalise_ms=r["normalise_ms"],
-                                           partition_locality_lambda=bench_lambda(),
-                                           pushed_rows_x_peers_fraction=r["push_fraction"],
-                                           rows_per_rank=r["n_pad"]),
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                         "kernel": "spmm_hop_kernel (per GPU; includes the fused NVLink pushes and the barrier)"},
-            "cpu_baseline": None, "e2e": r["e2e"], "gpu_launches": r["launches"], "clocks": r["clocks"],
-            # the same workload on ONE GPU of this box, measured by rank 0 in this run, so that the
-            # strong-scaling efficiency value / (n_gpus * single.value) can be read off this line
-            "single_gpu_same_workload": r["single"],
-            "other_workloads": extras,
-        }
-        print(json.dumps(line), flush=True)
-    dist.barrier()
-    dist.destroy_process_group()

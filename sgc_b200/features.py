@@ -148,6 +148,10 @@ class StandardizedFeatures(torch.Tensor):
             rows = raw[idx]
             if mean is None:
                 return rows
+            if rows.untyped_storage().data_ptr() == raw.untyped_storage().data_ptr():
+                # a slice is a view: parent and child each carry their own "applied" flag, so an in-place
+                # apply_() on one would standardise the shared storage twice for the other -> own copy
+                rows = rows.clone()
             if rows.dim() != 2:
                 return (rows - mean) / std
             return StandardizedFeatures(to_padded(rows) if rows.is_cuda else rows, mean, std)

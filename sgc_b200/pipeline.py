@@ -379,10 +379,10 @@ def precompute_host(adj, features, degree, standardize=False, out=None, out_bloc
                 standardize_(cur, mean, std)
             for k in range(degree - 1):
                 nxt = bufs[k & 1][:, c0:c1]
-                hop(graph, cur, chunk=chunk, out=nxt)
+                hop(graph, cur, chunk=chunk, out=nxt, pad_owned=True)
                 cur = nxt
             if blocks is None:
-                hop(graph, cur, chunk=chunk, out=y[:, c0:c1])
+                hop(graph, cur, chunk=chunk, out=y[:, c0:c1], pad_owned=by_cols and c1 == f)
                 back(0, n, c0, c1)
             else:
                 # last hop by row blocks, each block copied back while the next one is computed

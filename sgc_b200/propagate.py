@@ -75,7 +75,14 @@ def as_graph(adj):
     raise TypeError("adj must be an SgcGraph or a CUDA torch sparse tensor, got %r" % type(adj))
 
 
-def _hop_args(g, plan, x, ldx, y, ldy, f, partial, mean, std, std_mode, slab, hints, peers=None, peer_mask=None):
+def push_tile_tasks():
+    """Rows of a peer tile per group slot (SGC_B200_PUSH_ROWS; 0 = the library default of 8): consecutive
+    output rows that travel to a peer as ONE cp.async.bulk store when they are contiguous in the operand."""
+    return int(_ENV("SGC_B200_PUSH_ROWS", "0"))
+
+
+def _hop_args(g, plan, x, ldx, y, ldy, f, partial, mean, std, std_mode, slab, hints, peers=None, peer_mask=None,
+              pad_owned=False):
     a = _ffi.HopArgs()
     use_fused = g.fused and fused_norm()
     if g.fused and not use_fused:
@@ -84,11 +91,12 @@ def _hop_args(g, plan, x, ldx, y, ldy, f, partial, mean, std, std_mode, slab, hi
         if len(peers) > _ffi.MAX_PEERS:
             raise ValueError("at most %d peers" % _ffi.MAX_PEERS)
         a.n_peers = len(peers)
+        a.push_tile_tasks = push_tile_tasks()
         for i, ptr in enumerate(peers):
             a.peer_y_d[i] = int(ptr)
         if peer_mask is not None:
             a.peer_mask_d = _ffi.ptr(peer_mask)
-    flags = 0
+    flags = _ffi.HOP_PAD_OWNED if pad_owned else 0
     if use_fused:
         flags |= _ffi.HOP_FUSED_NORM
         a.aval_d, a.dinv_d, a.dinv_rows_d = _ffi.ptr(g.aval), _ffi.ptr(g.dinv), _ffi.ptr(g.dinv_rows)
@@ -124,10 +132,23 @@ def _partial(plan, f, dev):
     return torch.empty((plan.partial_rows, (f + 3) // 4 * 4), dtype=torch.float32, device=dev)
 
 
+def _check_out(g, out, f):
+    if not isinstance(out, torch.Tensor) or out.dim() != 2 or tuple(out.shape) != (g.n_rows, f):
+        raise ValueError("out must be a [%d, %d] tensor, got %r" % (g.n_rows, f, getattr(out, "shape", type(out))))
+    if out.dtype != torch.float32 or out.device != g.device:
+        raise ValueError("out must be a float32 tensor on %s (got %s on %s)" % (g.device, out.dtype, out.device))
+    if out.stride(1) != 1 or (out.shape[0] > 1 and out.stride(0) < f):
+        raise ValueError("out must have unit column stride and a row stride of at least F")
+
+
 def hop(adj, x, mean=None, std=None, chunk=None, slab=None, hints=None, std_mode=None, out=None, peers=None,
-        peer_mask=None):
+        peer_mask=None, pad_owned=False):
     """One hop ``S @ x`` (torch.spmm(adj, x), utils.py:95).  Returns a new [n_rows, F] fp32
     tensor.  With ``mean``/``std`` (fp32 [F]) the gathered operand is standardised on the fly.
+    ``out``: optional [n_rows, F] fp32 destination (any row stride >= F); only its columns [0, F) are
+    written, so it may be a column view of a wider live matrix -- unless ``pad_owned=True`` declares the
+    columns up to the next multiple of 4 to be padding of this operand (features.padded_rows storage), which
+    lets the kernel finish every row with whole 16-byte stores.
     ``peers``: device addresses of other GPUs' buffers (same row 0 and leading dimension as ``out``)
     that receive every output row from the kernel's epilogue (row-sharded propagation, dist.py);
     ``peer_mask`` (int32/uint32 [n_rows], optional): bit p set = row must go to peers[p]."""
@@ -135,6 +156,8 @@ def hop(adj, x, mean=None, std=None, chunk=None, slab=None, hints=None, std_mode
     dev = require_cuda(g.device)
     x = _check_features(g, x)
     f = int(x.shape[1])
+    if out is not None:
+        _check_out(g, out, f)
     if mean is not None:
         mean, std = mean.to(dev, torch.float32).contiguous(), std.to(dev, torch.float32).contiguous()
     with torch.cuda.device(dev):
@@ -146,7 +169,7 @@ def hop(adj, x, mean=None, std=None, chunk=None, slab=None, hints=None, std_mode
         partial = _partial(plan, f, dev)
         a = _hop_args(g, plan, x.data_ptr(), x.stride(0), y.data_ptr(), y.stride(0), f, partial, mean, std,
                       std_mode or default_std_mode(), default_slab() if slab is None else slab,
-                      default_hints() if hints is None else hints, peers, peer_mask)
+                      default_hints() if hints is None else hints, peers, peer_mask, pad_owned)
         _ffi.call("sgc_spmm_hop", plan.handle, _ffi.ctypes.byref(a), stream_ptr())
     return y
 

@@ -201,3 +201,40 @@ def make_shape(name, device="cpu", scale=1.0, lam=0.0, row_range=None, seed=0, w
         x = gaussian_features(n, s["f"], seed=seed + 1, scaled=s["scaled"], row_range=row_range,
                               device=device)
     return dict(n=n, f=s["f"], k=s["k"], row_ptr=row_ptr, col=col, val=val, x=x)
+
+
+def write_reddit_npz(out_dir, n=24_000, f=602, n_classes=41, pairs_per_node=25, lam=0.85, seed=0,
+                     signal=1.5, splits=(0.66, 0.10, 0.24)):
+    """Synthetic Reddit in the file layout `utils.loadRedditFromNPZ` reads (/root/reference/utils.py:104-108),
+    so that the reference's reddit.py and this repo's drop-in run on identical files:
+
+        reddit_adj.npz   scipy CSR (save_npz), symmetric 0/1 adjacency, no self-loops
+        reddit.npz       feats fp32 [N, F] (NOT standardised), y_train / y_val / y_test (int labels),
+                         train_index / val_index / test_index (int64 node ids)
+
+    41 planted communities: class = contiguous block id (`planted_labels`), a fraction `lam` of every node's
+    neighbours drawn from its own block; features = per-column scale/offset as in `gaussian_features(scaled=True)`
+    plus a class centroid of strength `signal` (so that K-hop propagated features are linearly separable but
+    not trivially so).  Splits: random permutation with seed+2 (~66 % / 10 % / 24 %)."""
+    import os
+
+    import numpy as np
+    import scipy.sparse as sp
+    row_ptr, col, _ = powerlaw_graph(n, n * pairs_per_node, alpha=1.3, cap=max(8, n // 12), seed=seed, lam=lam,
+                                     blocks=n_classes, symmetric=True, device="cpu")
+    adj = sp.csr_matrix((np.ones(col.numel(), dtype=np.float64), col.numpy(), row_ptr.numpy()), shape=(n, n))
+    labels = planted_labels(n, n_classes).numpy()
+    x = gaussian_features(n, f, seed=seed + 1, scaled=True, device="cpu").numpy()
+    cols = torch.arange(f, dtype=torch.int64)
+    scale = (0.1 + 4.9 * hash_uniform(seed + 1, 100, cols)).numpy()           # the per-column s_f of gaussian_features
+    cent = hash_normal(seed + 3, 7, torch.arange(n_classes * f, dtype=torch.int64)).view(n_classes, f).numpy()
+    x = (x + signal * cent[labels] * scale[None, :]).astype(np.float32)
+    perm = np.random.RandomState(seed + 2).permutation(n)
+    n_tr, n_va = int(splits[0] * n), int(splits[1] * n)
+    tr, va, te = np.sort(perm[:n_tr]), np.sort(perm[n_tr:n_tr + n_va]), np.sort(perm[n_tr + n_va:])
+    os.makedirs(out_dir, exist_ok=True)
+    sp.save_npz(os.path.join(out_dir, "reddit_adj.npz"), adj)
+    np.savez(os.path.join(out_dir, "reddit.npz"), feats=x, y_train=labels[tr], y_val=labels[va], y_test=labels[te],
+             train_index=tr.astype(np.int64), val_index=va.astype(np.int64), test_index=te.astype(np.int64))
+    return {"n": n, "f": f, "nnz": int(adj.nnz), "classes": n_classes, "train": int(tr.size), "val": int(va.size),
+            "test": int(te.size)}

@@ -88,28 +88,30 @@ def test_hop_pushes_rows_to_peer_buffers():
     s = synth.make_shape("reddit", device=dev, scale=0.02, seed=5)
     n = s["n"]
     g = sgc_b200.normalize_csr(n, s["row_ptr"], s["col"], s["val"])
-    for f in (100, 130, 602, 7):
+    for f, tile_rows in ((100, "0"), (100, "1"), (100, "4"), (100, "16"), (130, "0"), (602, "0"), (7, "0"), (7, "3"), (64, "0")):
+        monkey_env("SGC_B200_PUSH_ROWS", tile_rows)
         ld = (f + 7) // 8 * 8
         x = s["x"][:, :f].contiguous()
         want = sgc_b200.hop(g, x, chunk=64)
         bufs = [torch.full((n + 3, ld), -7.0, device=dev) for _ in range(3)]
         own, peers = bufs[0], bufs[1:]
-        sgc_b200.hop(g, x, chunk=64, out=own[2:2 + n, :f], peers=[p[2:].data_ptr() for p in peers])
+        sgc_b200.hop(g, x, chunk=64, out=own[2:2 + n, :f], peers=[p[2:].data_ptr() for p in peers], pad_owned=True)
         for b in bufs:
-            assert torch.equal(b[2:2 + n, :f], want)
+            assert torch.equal(b[2:2 + n, :f], want), (f, tile_rows)
             assert bool((b[:2] == -7.0).all()) and bool((b[2 + n:] == -7.0).all())
             pad = b[2:2 + n, f:]                  # pad columns: untouched, or zero-filled by the bulk store
             assert bool(((pad == -7.0) | (pad == 0.0)).all())
         # halo mask: a row reaches peer p only if bit p of its mask is set
         mask = torch.randint(0, 4, (n,), dtype=torch.int32, device=dev)
+        mask[: n // 3] = 3                        # long runs of rows every peer needs: the tile-store path
         bufs = [torch.full((n + 3, ld), -7.0, device=dev) for _ in range(3)]
         sgc_b200.hop(g, x, chunk=64, out=bufs[0][2:2 + n, :f], peers=[p[2:].data_ptr() for p in bufs[1:]],
-                     peer_mask=mask)
+                     peer_mask=mask, pad_owned=True)
         assert torch.equal(bufs[0][2:2 + n, :f], want)
         for slot, b in enumerate(bufs[1:]):
             sent = ((mask >> slot) & 1).bool()
-            assert torch.equal(b[2:2 + n, :f][sent], want[sent])
-            assert bool((b[2:2 + n][~sent] == -7.0).all())
+            assert torch.equal(b[2:2 + n, :f][sent], want[sent]), (f, tile_rows, slot)
+            assert bool((b[2:2 + n][~sent] == -7.0).all()), (f, tile_rows, slot)
         # unaligned output (odd leading dimension): the per-lane store fallback
         ldu = f + 1 if (f + 1) % 2 else f + 2
         bufs = [torch.full((n + 3, ldu), -7.0, device=dev) for _ in range(3)]
@@ -117,6 +119,46 @@ def test_hop_pushes_rows_to_peer_buffers():
         for b in bufs:
             assert torch.equal(b[1:1 + n, :f], want)
             assert bool((b[:1] == -7.0).all()) and bool((b[1 + n:] == -7.0).all()) and bool((b[:, f:] == -7.0).all())
+    monkey_env("SGC_B200_PUSH_ROWS", None)
+    # widths that are not a multiple of 4 floats cannot be bulk-pushed into operands whose padding is not owned
+    x = s["x"][:, :130].contiguous()
+    bufs = [torch.zeros((n, 136), device=dev) for _ in range(2)]
+    with pytest.raises(sgc_b200._ffi.SgcError):
+        sgc_b200.hop(g, x, out=bufs[0][:, :130], peers=[bufs[1].data_ptr()])
+
+
+def monkey_env(key, value):
+    if value is None:
+        os.environ.pop(key, None)
+    else:
+        os.environ[key] = value
+
+
+def test_hop_out_column_view_leaves_neighbours_alone():
+    """hop(out=big[:, :f]) writes columns [0, f) only: the columns of a wider live matrix next to the view
+    keep their values unless pad_owned=True hands the pad columns to the kernel."""
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    import sgc_b200
+    from sgc_b200 import synth
+    dev = torch.device("cuda", 0)
+    s = synth.make_shape("reddit", device=dev, scale=0.01, seed=3)
+    n = s["n"]
+    g = sgc_b200.normalize_csr(n, s["row_ptr"], s["col"], s["val"])
+    for f, width in ((30, 32), (30, 40), (101, 104), (7, 8), (601, 608)):
+        x = s["x"][:, :f].contiguous()
+        want = sgc_b200.hop(g, x, chunk=64)
+        big = torch.full((n, width), 5.0, device=dev)
+        sgc_b200.hop(g, x, chunk=64, out=big[:, :f])
+        assert torch.equal(big[:, :f], want) and bool((big[:, f:] == 5.0).all()), (f, width)
+        big = torch.full((n, width), 5.0, device=dev)
+        sgc_b200.hop(g, x, chunk=64, out=big[:, :f], pad_owned=True)
+        r4 = (f + 3) // 4 * 4
+        assert torch.equal(big[:, :f], want) and bool((big[:, r4:] == 5.0).all())
+    with pytest.raises(ValueError):
+        sgc_b200.hop(g, x, out=torch.empty((n, 5), device=dev))
+    with pytest.raises(ValueError):
+        sgc_b200.hop(g, x, out=torch.empty((n, x.shape[1]), device=dev, dtype=torch.float64))
 
 
 def test_push_rows_kernel():
