@@ -60,10 +60,12 @@ int32_t sgc_l2_set_persisting_bytes(int64_t bytes, int64_t *granted_out);
 /* Measurement aid (bench.py `roofline.l2`, tools/l2_peak.py): reads the `bytes` (multiple of 512) at buf_d
  * `reps` times from all SMs in 512-byte pieces (32 lanes x 16 bytes, the hop kernel's gather shape) with L1
  * allocation off -- with a buffer that stays resident in the 126 MB L2 the CUDA-event time of this launch is
- * the L2 -> SM read bandwidth of the box.  pattern 0: pieces in address order, 1: hashed order.  sink_d: one
+ * the L2 -> SM read bandwidth of the box.  pattern 0: pieces in address order, 1: hashed order (the gather's).
+ * piece_stride_bytes: distance between pieces (0 = 512, contiguous; 2432 = one 128-float slab of 608-float rows:
+ * the Reddit-shaped hop's footprint -- bytes then spans the strided range, of which 512/stride is read).  sink_d: one
  * float the kernel may write (keeps the loads alive).  No counterpart in the reference. */
-int32_t sgc_l2_read_probe(const void *buf_d, int64_t bytes, int32_t reps, int32_t pattern,
-                          int32_t ctas_per_sm, float *sink_d, void *stream);
+int32_t sgc_l2_read_probe(const void *buf_d, int64_t bytes, int64_t piece_stride_bytes, int32_t reps,
+                          int32_t pattern, int32_t ctas_per_sm, float *sink_d, void *stream);
 
 /* ---- column-slab transfers (utils.py:82-88,126-130: the reference's .cuda() / .cpu() copies) -------
  * Strided 2-D copy on the DMA engines (cudaMemcpy2DAsync, direction inferred from the pointers):

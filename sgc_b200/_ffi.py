@@ -42,7 +42,7 @@ SIGNATURES = {
     "sgc_device_check": (c_i32, [c_i32]),
     "sgc_launch_count": (c_i64, []),
     "sgc_l2_set_persisting_bytes": (c_i32, [c_i64, ctypes.POINTER(c_i64)]),
-    "sgc_l2_read_probe": (c_i32, [c_p, c_i64, c_i32, c_i32, c_i32, c_p, c_p]),
+    "sgc_l2_read_probe": (c_i32, [c_p, c_i64, c_i64, c_i32, c_i32, c_i32, c_p, c_p]),
     "sgc_copy_2d": (c_i32, [c_p, c_i64, c_p, c_i64, c_i64, c_i64, c_p]),
     "sgc_host_all_equal_f64": (c_i32, [c_p, c_i64, ctypes.c_double, c_i32, c_i64]),
     "sgc_scan_workspace_bytes": (c_sz, [c_i64]),

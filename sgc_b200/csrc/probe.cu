@@ -22,8 +22,8 @@ __device__ __forceinline__ float4 ld_l2_v4(const float4 *p)
 
 // pattern 0: pieces in address order (grid-stride); pattern 1: pieces in a hashed order (the gather's).
 __global__ void __launch_bounds__(PROBE_THREADS)
-l2_read_probe_kernel(const float4 *__restrict__ buf, int64_t n_pieces, int32_t reps, int32_t pattern,
-                     float *__restrict__ sink)
+l2_read_probe_kernel(const float4 *__restrict__ buf, int64_t n_pieces, int64_t stride_v4, int32_t reps,
+                     int32_t pattern, float *__restrict__ sink)
 {
     const int lane = threadIdx.x & 31;
     const int64_t warp = (int64_t)blockIdx.x * (PROBE_THREADS / 32) + (threadIdx.x >> 5);
@@ -39,9 +39,9 @@ l2_read_probe_kernel(const float4 *__restrict__ buf, int64_t n_pieces, int32_t r
                 if (pattern == 1) {
                     uint64_t z = (uint64_t)p * 0x9E3779B97F4A7C15ull + (uint64_t)r * 0xD1B54A32D192ED03ull;
                     z ^= z >> 29;
-                    p = (int64_t)(z % (uint64_t)n_pieces);
+                    p = (int64_t)(((z >> 32) * (uint64_t)n_pieces) >> 32);      // n_pieces < 2^32
                 }
-                v[u] = ld_l2_v4(buf + p * 32 + lane);
+                v[u] = ld_l2_v4(buf + p * stride_v4 + lane);
             }
 #pragma unroll
             for (int u = 0; u < PROBE_UNROLL; ++u) acc += v[u].x + v[u].y + v[u].z + v[u].w;
@@ -56,17 +56,20 @@ using namespace sgc;
 
 extern "C" {
 
-int32_t sgc_l2_read_probe(const void *buf_d, int64_t bytes, int32_t reps, int32_t pattern,
-                          int32_t ctas_per_sm, float *sink_d, void *stream)
+int32_t sgc_l2_read_probe(const void *buf_d, int64_t bytes, int64_t piece_stride_bytes, int32_t reps,
+                          int32_t pattern, int32_t ctas_per_sm, float *sink_d, void *stream)
 {
+    if (piece_stride_bytes <= 0) piece_stride_bytes = 512;
+    SGC_REQUIRE(piece_stride_bytes >= 512 && piece_stride_bytes % 16 == 0, "l2_read_probe: bad piece stride");
     SGC_REQUIRE(buf_d && sink_d, "l2_read_probe: null pointer");
-    SGC_REQUIRE((reinterpret_cast<uintptr_t>(buf_d) & 15) == 0 && bytes >= 512 && bytes % 512 == 0,
-                "l2_read_probe: buffer must be 16-byte aligned and a multiple of 512 bytes");
+    SGC_REQUIRE((reinterpret_cast<uintptr_t>(buf_d) & 15) == 0 && bytes >= 512,
+                "l2_read_probe: buffer must be 16-byte aligned and hold at least one 512-byte piece");
     SGC_REQUIRE(reps >= 1 && (pattern == 0 || pattern == 1), "l2_read_probe: bad reps / pattern");
     if (ctas_per_sm < 1) ctas_per_sm = 8;
     const int grid = sm_count() * ctas_per_sm;
     l2_read_probe_kernel<<<grid, PROBE_THREADS, 0, as_stream(stream)>>>(
-        reinterpret_cast<const float4 *>(buf_d), bytes / 512, reps, pattern, sink_d);
+        reinterpret_cast<const float4 *>(buf_d), (bytes - 512) / piece_stride_bytes + 1, piece_stride_bytes / 16, reps,
+        pattern, sink_d);
     SGC_LAUNCH_CHECK();
     return SGC_OK;
 }

@@ -82,10 +82,18 @@ def reddit_f1(out):
 
 
 def test_reddit_py_f1_unchanged(tmp_path):
-    """reddit.py --inductive --test on a synthetic Reddit (41 planted communities, files in the layout of
-    utils.py:104-108), once on the reference's stock CUDA path and once through the drop-in: the printed test F1
-    (reddit.py:70-72, metrics.py:9-15) must be the same to its 4 printed decimals.  Also the transductive
-    variant (reddit.py:47: processed_features[idx_train] with ndarray indices)."""
+    """reddit.py on a synthetic Reddit (41 planted communities, files in the layout of utils.py:104-108), on the
+    reference's stock CUDA path and through the drop-in; test F1 as printed (reddit.py:70-72, metrics.py:9-15).
+
+    What "unchanged" can mean here was measured first (tools/reddit_f1_diag.py, profiles/r02_reddit_f1_diag.log):
+    the reference's CUDA path is NOT deterministic -- torch.spmm on a COO tensor accumulates with atomics, its
+    propagated features differ by 1.4e-6 from one run to the next -- and with the script's default of 2 LBFGS
+    epochs the optimiser is far from converged, so the reference's own F1 scatters from run to run (0.58 / 0.97 /
+    0.60 for --inductive --test).  With --epochs 10 LBFGS is near the optimum and the reference reproduces
+    itself to ~0.003.  So: at --epochs 10 the drop-in's F1 must lie within the reference's own run-to-run band
+    (mean of 3 stock runs +- max(3 x their spread, 0.005)); the drop-in itself must print the SAME F1 on every
+    run (it is deterministic); and at the default 2 epochs it must lie inside the reference's observed range
+    widened by the same margin."""
     need_staged()
     sys.path.insert(0, REPO)
     from sgc_b200 import synth
@@ -99,12 +107,21 @@ def test_reddit_py_f1_unchanged(tmp_path):
         os.symlink(str(data), d / "data")
     assert which_modules(stock, False) == [str(stock), str(stock)]
     assert which_modules(dropin, True) == [REPO, REPO]
-    for flags in (["--inductive", "--test"], ["--test"], []):
-        ref_out = run_script(stock, ["reddit.py"] + flags, drop_in=False)
-        own_out = run_script(dropin, ["reddit.py"] + flags, drop_in=True)
-        f_ref, f_own = reddit_f1(ref_out), reddit_f1(own_out)
-        assert 0.5 < float(f_ref) <= 1.0, ref_out          # the planted communities are learnable, not degenerate
-        assert f_own == f_ref, (flags, ref_out[-300:], own_out[-300:])
+    for flags in (["--inductive", "--test"], ["--test"]):
+        fl = flags + ["--epochs", "10"]
+        ref = [float(reddit_f1(run_script(stock, ["reddit.py"] + fl, drop_in=False))) for _ in range(3)]
+        own = [reddit_f1(run_script(dropin, ["reddit.py"] + fl, drop_in=True)) for _ in range(2)]
+        assert own[0] == own[1], (flags, own)                          # deterministic
+        assert min(ref) > 0.9, (flags, ref)                            # learnable, not degenerate
+        mean, spread = sum(ref) / len(ref), max(ref) - min(ref)
+        assert abs(float(own[0]) - mean) <= max(3 * spread, 0.005), (flags, ref, own)
+    # the script's defaults (2 epochs, transductive, validation F1: reddit.py:47,49 index with ndarrays)
+    ref = [float(reddit_f1(run_script(stock, ["reddit.py"], drop_in=False))) for _ in range(3)]
+    own = [reddit_f1(run_script(dropin, ["reddit.py"], drop_in=True)) for _ in range(2)]
+    assert own[0] == own[1], own
+    # 2 epochs: the stock runs scatter by 0.1-0.4 between themselves (bimodal), so the band is wide by nature
+    margin = max(3 * (max(ref) - min(ref)), 0.15)
+    assert min(ref) - margin <= float(own[0]) <= min(1.0, max(ref) + margin) and float(own[0]) > 0.5, (ref, own)
 
 
 HYPEROPT_STUB = '''

@@ -22,7 +22,7 @@ for mb in (8, 16, 32, 48, 64, 96, 128, 256, 1024):
     reps = max(2, 2048 // mb)
     for pattern in (0, 1):
         for ctas in (4, 8):
-            call = lambda: _ffi.call("sgc_l2_read_probe", buf.data_ptr(), buf.numel() * 4, reps, pattern, ctas,
+            call = lambda: _ffi.call("sgc_l2_read_probe", buf.data_ptr(), buf.numel() * 4, 0, reps, pattern, ctas,
                                      sink.data_ptr(), torch.cuda.current_stream().cuda_stream)
             call()
             torch.cuda.synchronize()
@@ -36,3 +36,24 @@ for mb in (8, 16, 32, 48, 64, 96, 128, 256, 1024):
             print("%8d %8s %6d %10.3f %10.0f" % (mb, "address" if pattern == 0 else "hashed", ctas, ms,
                                                  mb * 1024 * 1024 * reps / (ms * 1e-3) / 1e9), flush=True)
     del buf
+
+# the Reddit-shaped hop's footprint: 512-byte pieces (one 128-float slab) of 232,965 rows at a 2432-byte pitch
+n, pitch = 232965, 2432
+buf = torch.ones(n * pitch // 4, dtype=torch.float32, device=dev)
+print("strided: %d pieces of 512 B at a %d-byte pitch (%.0f MB touched in %.0f MB)" % (n, pitch, n * 512 / 1e6, n * pitch / 1e6))
+for pattern in (0, 1):
+    for ctas in (4, 7, 8):
+        reps = 20
+        call = lambda: _ffi.call("sgc_l2_read_probe", buf.data_ptr(), buf.numel() * 4, pitch, reps, pattern, ctas,
+                                 sink.data_ptr(), torch.cuda.current_stream().cuda_stream)
+        call()
+        torch.cuda.synchronize()
+        ts = []
+        for _ in range(5):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(); call(); b.record()
+            torch.cuda.synchronize()
+            ts.append(a.elapsed_time(b))
+        ms = min(ts)
+        print("%8s %8s %6d %10.3f %10.0f" % ("slab", "address" if pattern == 0 else "hashed", ctas, ms,
+                                             n * 512 * reps / (ms * 1e-3) / 1e9), flush=True)
