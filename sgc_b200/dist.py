@@ -425,8 +425,8 @@ def verify_against_single(y_local, y_single, row0, col0, f_total, group=None):
     r, c = int(y_local.shape[0]), int(y_local.shape[1])
     mine = torch.stack([torch.tensor(v, dtype=torch.int64, device=dev) for v in (row0, r, col0, c)]
                        + [block_checksum(y_local, row0, col0, f_total)])
-    allv = torch.empty(world * 5, dtype=torch.int64, device=dev)
-    dist.all_gather_into_tensor(allv, mine, group=group)
+    allv = torch.empty((world * 5, 1), dtype=torch.int64, device=dev)
+    _all_gather(allv, mine.view(5, 1), group, False)
     allv = allv.view(world, 5).cpu().tolist()
     ok = torch.ones(world, dtype=torch.int64, device=dev)
     if rank == 0:

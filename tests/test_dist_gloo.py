@@ -162,3 +162,104 @@ def test_shared_adjacency_pieces_and_common_verdict(world):
         assert all(0 <= hi - lo <= per for lo, hi, _, _ in spans)
     for r in range(world):
         assert ret[r][1] == [2.0, None, None, None, None, 2.0, None], (r, ret[r][1])
+
+
+def test_block_checksum_is_partition_independent_and_bit_sensitive():
+    """dist.block_checksum: the sum over the blocks of any partition equals the checksum of the whole matrix
+    (wrap-around int64), and any single-bit change anywhere -- including +0.0 vs -0.0 and element swaps --
+    changes it."""
+    from sgc_b200.dist import block_checksum
+    torch.manual_seed(0)
+    y = torch.randn(57, 23)
+    f = y.shape[1]
+    whole = int(block_checksum(y, 0, 0, f))
+    M = (1 << 64)
+    rows = sum(int(block_checksum(y[a:b], a, 0, f)) for a, b in ((0, 10), (10, 11), (11, 57))) % M
+    cols = sum(int(block_checksum(y[:, a:b], 0, a, f, chunk_elems=64)) for a, b in ((0, 16), (16, 23))) % M
+    assert rows == whole % M and cols == whole % M
+    z = y.clone()
+    z[31, 7] = torch.nextafter(z[31, 7], torch.tensor(10.0))
+    assert int(block_checksum(z, 0, 0, f)) != whole
+    z = y.clone()
+    z[3, 4], z[3, 5] = y[3, 5], y[3, 4]
+    assert int(block_checksum(z, 0, 0, f)) != whole
+    zero = torch.zeros(4, 4)
+    neg = zero.clone()
+    neg[2, 2] = -0.0
+    assert int(block_checksum(zero, 0, 0, 4)) != int(block_checksum(neg, 0, 0, 4))
+    assert int(block_checksum(y[:0], 0, 0, f)) == 0
+
+
+def verify_worker(rank, world, port, corrupt, by_cols, ret):
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from sgc_b200 import dist as sd
+        torch.manual_seed(1)
+        y = torch.randn(41, 19)
+        if by_cols:
+            c0, c1 = sd.partition_features(19, world, unit=4)[rank]
+            mine, r0 = y[:, c0:c1].clone(), 0
+        else:
+            _, parts = sd.partition_rows(41, world)
+            r0, r1 = parts[rank]
+            mine, c0 = y[r0:r1].clone(), 0
+        if corrupt == rank and mine.numel():
+            mine.view(-1)[mine.numel() // 2] *= (1 + 2 ** -23)           # one ulp, one element, one rank
+        rep = sd.verify_against_single(mine, y if rank == 0 else None, r0, c0, 19)
+        ret[rank] = (rep["ok"], rep["per_rank"], rep["checksum"])
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,by_cols", [(2, False), (3, False), (2, True)])
+def test_verify_against_single_flags_the_rank_that_differs(world, by_cols):
+    """dist.verify_against_single (what every bench.py --gpus N leg runs after its timed steps): all ranks
+    agree on the verdict; a one-ulp deviation of one element on one rank is found and attributed."""
+    for corrupt in (-1, world - 1):
+        ret = mp.Manager().dict()
+        mp.spawn(verify_worker, args=(world, free_port(), corrupt, by_cols, ret), nprocs=world, join=True)
+        want = [r != corrupt for r in range(world)]
+        for rank in range(world):
+            ok, per_rank, checksum = ret[rank]
+            assert per_rank == want and ok == all(want), (corrupt, rank, per_rank)
+            assert checksum == ret[0][2]
+
+
+def replication_worker(rank, world, port, ret):
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from sgc_b200 import dist as sd
+        from sgc_b200.graph import SgcGraph
+        indptr, indices, data, x = make_problem()
+        n, f = x.shape
+        n_pad, parts = sd.partition_rows(n, world)
+        row0, row1 = parts[rank]
+        b, e = indptr[row0], indptr[row1]
+        g = SgcGraph(row1 - row0, world * n_pad, torch.from_numpy(indptr[row0:row1 + 1] - b),
+                     torch.from_numpy(indices[b:e]), None, None, sval=torch.from_numpy(data[b:e]))
+        sg = sd.ShardedGraph(g, rank, world, n, n_pad, row0, row1)
+        prop = sd.ShardedPropagator(sg, f, row_blocks=2, hop_fn=lambda *a: None)
+        prop.load(torch.from_numpy(x[row0:row1].copy()))
+        clean = sd._replication_mismatches(prop, prop.buf[0], False, 1000, None)
+        masked = sd._replication_mismatches(prop, prop.buf[0], True, 1000, None)
+        if rank == 1:                                  # a stale copy of one of rank 0's rows, on rank 1 only
+            victim = int(indices[indptr[row0]:indptr[row1]][indices[indptr[row0]:indptr[row1]] < parts[0][1]][0])
+            prop.buf[0][victim, 3] += 1.0
+        dirty = sd._replication_mismatches(prop, prop.buf[0], True, 1000, None)
+        ret[rank] = (clean, masked, dirty)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_replication_check_finds_a_stale_pushed_row():
+    """dist._replication_mismatches (part of verify_sharded): owner-vs-copy comparison of sampled rows of the
+    full-height operand, restricted to the rows a rank's shard gathers when halo masks are in use."""
+    world = 2
+    ret = mp.Manager().dict()
+    mp.spawn(replication_worker, args=(world, free_port(), ret), nprocs=world, join=True)
+    for rank in range(world):
+        clean, masked, dirty = ret[rank]
+        assert clean[0] == 0 and clean[1] > 0 and masked[0] == 0 and 0 < masked[1] <= clean[1]
+        assert dirty[0] == 1 and dirty[1] == masked[1]
