@@ -210,7 +210,7 @@ def run_reference(args):
     feature columns) -- torch.spmm's cost on the CPU has a large per-call part (it sorts/coalesces the COO
     tensor the reference's loader builds, every hop), so a row or column sample would misstate the rate.
     A whole step takes ~10-20 s on the host cores; when steps+warmup of them exceed the time budget
-    (SGC_BENCH_REF_BUDGET_S, default 150 s) fewer whole steps are timed and the line says so: `steps` is the
+    (SGC_BENCH_REF_BUDGET_S, default 90 s) fewer whole steps are timed and the line says so: `steps` is the
     number actually timed, `details.steps_requested` what the command asked for."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -236,7 +236,7 @@ def run_reference(args):
     standardise_s = time.perf_counter() - t0
     del s
 
-    budget = float(os.environ.get("SGC_BENCH_REF_BUDGET_S", "150"))
+    budget = float(os.environ.get("SGC_BENCH_REF_BUDGET_S", "90"))
     warm_times = []
     for _ in range(min(args.warmup, 1)):                 # one whole step; more warm-up is pointless at ~10 s a step
         _, secs = ref.sgc_precompute(x, adj, k)

@@ -407,7 +407,7 @@ def bench(args, rank, world, dev, B):
     if extra_names is None:
         extra_names = "" if args.workload_given else ("products,papers100m" if world >= 8 else "products")
     lams = [float(v) for v in os.environ.get("SGC_BENCH_LAMBDAS", "0,0.8").split(",") if v != ""]
-    papers_budget = float(os.environ.get("SGC_BENCH_PAPERS_BUDGET_S", "420"))
+    papers_budget = float(os.environ.get("SGC_BENCH_PAPERS_BUDGET_S", "300"))
     for other in [e for e in extra_names.split(",") if e and e != name]:
         for lam in lams:
             key = other if lam == 0 else "%s_lambda%g" % (other, lam)

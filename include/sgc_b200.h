@@ -203,7 +203,9 @@ typedef struct sgc_plan sgc_plan_t;
  * in L2 (0 = library default for the shape). */
 size_t  sgc_spmm_plan_workspace_bytes(int64_t n_rows, int64_t nnz, int32_t chunk);
 /* Builds the split table on `stream`; SYNCHRONISES the stream once to read back the item count.
- * The plan keeps pointers into ws_d and to row_ptr_d/col_d: they must outlive the plan. */
+ * The plan keeps pointers into ws_d and to row_ptr_d/col_d: they must outlive the plan.  The first 256 bytes
+ * of ws_d are the ticket counter of the multi-GPU hop (K5), reset on the hop's stream before each launch:
+ * a plan serves ONE hop with peers at a time (hops on different streams need their own plans). */
 int32_t sgc_spmm_plan_create(int64_t n_rows, int64_t n_cols, int64_t nnz,
                              const int64_t *row_ptr_d, const int32_t *col_d, int32_t chunk,
                              void *ws_d, size_t ws_bytes, sgc_plan_t **plan_out, void *stream);

@@ -124,6 +124,7 @@ hot_tag_kernel(int64_t nnz, const int32_t *__restrict__ col, const uint32_t *__r
 static inline size_t align256(size_t v) { return (v + 255) / 256 * 256; }
 
 struct PlanLayout {
+    size_t off_counter;          // 256 bytes: the peer variant's tile ticket counter
     size_t off_chunks, off_long, off_scan, scan_bytes;
     size_t off_li_row, off_li_len, off_li_beg, off_lr_row, off_lr_cnt, off_lr_first, total;
     int64_t max_items, max_long;
@@ -132,10 +133,11 @@ struct PlanLayout {
 static PlanLayout plan_layout(int64_t n_rows, int64_t nnz, int32_t chunk)
 {
     PlanLayout L{};
-    if (chunk <= 0) { L.total = 256; return L; }
+    L.off_counter = 0;
+    if (chunk <= 0) { L.total = 512; return L; }
     L.max_long = nnz / chunk + 1;
     L.max_items = 2 * (nnz / chunk) + 2;
-    size_t o = 0;
+    size_t o = 256;
     L.off_chunks = o; o += align256((size_t)(n_rows + 1) * 8);
     L.off_long = o;   o += align256((size_t)(n_rows + 1) * 8);
     L.scan_bytes = scan_workspace_bytes(n_rows + 1);
@@ -272,6 +274,10 @@ static int32_t run_hop(const sgc_plan_impl *pl, const sgc_hop_args_t *a, const f
         p.tpw = tpw;
         // tiles are contiguous in y when one slab covers the whole padded row
         p.stage_stride = (p.n_slabs == 1 && ldy <= slab && y_vec == 4) ? (int32_t)ldy : slab;
+        SGC_REQUIRE(pl->tile_counter != nullptr, "spmm_hop: the plan has no workspace (needed by the peer variant)");
+        p.tile_counter = pl->tile_counter;
+        // one plan = one hop in flight: the counter is reset on the hop's own stream right before its launch
+        SGC_CUDA_TRY(cudaMemsetAsync(p.tile_counter, 0, sizeof(unsigned long long), s));
     }
     const int64_t n_tasks = (int64_t)p.n_slabs * (p.n_long_items + p.n_rows);
     int32_t rc = fn(p, n_tasks, s);
@@ -350,12 +356,15 @@ int32_t sgc_spmm_plan_create(int64_t n_rows, int64_t n_cols, int64_t nnz,
         set_error("spmm_plan_create: workspace too small (%zu < %zu)", ws_bytes, L.total);
         return SGC_ERR_WORKSPACE;
     }
+    // the first 256 bytes of the workspace hold the peer variant's ticket counter (when there is a workspace)
+    const bool has_counter = ws_d != nullptr && ws_bytes >= 256;
     cudaStream_t s = as_stream(stream);
     sgc_plan *pl = new (std::nothrow) sgc_plan();
     SGC_REQUIRE(pl, "spmm_plan_create: out of host memory");
     sgc_plan_impl &P = pl->impl;
     P.n_rows = n_rows; P.n_cols = n_cols; P.nnz = nnz;
     P.row_ptr = row_ptr_d; P.col = col_d; P.chunk = chunk;
+    P.tile_counter = has_counter ? reinterpret_cast<unsigned long long *>(ws_d) : nullptr;
     if (chunk > 0 && n_rows > 0) {
         char *ws = reinterpret_cast<char *>(ws_d);
         int64_t *n_chunks = reinterpret_cast<int64_t *>(ws + L.off_chunks);

@@ -56,6 +56,7 @@ struct HopDev {
                          // the pad columns belong to the operand; else == f and tails go element-wise)
     int32_t tpw;         // K5: tasks per tile and group slot of the peer variant (rows per tile = tpw * 32/G)
     int32_t stage_stride;// K5: floats between staged rows (ldy when tiles are contiguous in y, else the slab width)
+    unsigned long long *tile_counter;   // K5: next tile to hand out (zeroed by the host before the launch)
     int32_t n_peers;     // K5: copies of y in other GPUs' memory that receive every output row
     float *peer_y[SGC_MAX_PEERS];
     const uint32_t *peer_mask;   // per-row bit set of peers that need the row (null: all)
@@ -73,6 +74,7 @@ struct sgc_plan_impl {
     const int32_t *lr_row;
     const int64_t *lr_first;
     const int32_t *lr_cnt;
+    unsigned long long *tile_counter;   // 8 bytes at the head of the plan workspace (peer variant's tickets)
     const int32_t *col_tagged;   // col with bit 31 set on "hot" columns (sgc_spmm_plan_tag_hot), or null
     int64_t n_hot_cols;
     int32_t hot_threshold;
@@ -361,9 +363,11 @@ spmm_hop_kernel(const HopDev p)
 // K5: the hop with the NVLink exchange fused in.  Every output row also goes to each peer's copy of the next
 // hop's gathered operand, inside this kernel, while other warps are still gathering.
 //
-// Persistent grid (one wave of CTAs); a warp walks TILES of RT = tpw * GPW consecutive tasks.  The output
-// rows of a tile are staged in shared memory and handed to the TMA unit as cp.async.bulk shared -> global
-// stores, so the LSU never waits on NVLink:
+// Persistent grid (one wave of CTAs); every warp draws TILES of RT = tpw * GPW consecutive tasks from a global
+// ticket counter (rows of a power-law graph differ in cost by orders of magnitude: a static split of the tiles
+// over the warps left a 15 % tail, measured at 2 GPUs; tickets are handed out in task order, so the rows being
+// gathered at any time are still neighbours in the CSR).  The output rows of a tile are staged in shared
+// memory and handed to the TMA unit as cp.async.bulk shared -> global stores, so the LSU never waits on NVLink:
 //   * tile store: when the tile is RT consecutive rows of y, all computed here, and a peer needs all of
 //     them, ONE bulk store of RT * ldy * 4 bytes goes to that peer (rows are contiguous in the operand,
 //     pad columns included).  Measured 8-GPU all-to-all: 416-byte stores 578 GB/s per GPU, 1.6 KB 641,
@@ -386,8 +390,6 @@ spmm_hop_peers_kernel(const HopDev p, const int64_t n_tiles)
     const int lane = threadIdx.x & 31;
     const int gl = lane % G;
     const int wic = threadIdx.x >> 5;
-    const int64_t warp = (int64_t)blockIdx.x * WARPS + wic;
-    const int64_t n_warps = (int64_t)gridDim.x * WARPS;
     const uint64_t pol_x = l2_policy(HOT ? 2 : ((p.hints & 1) ? 1 : 0));
     const uint64_t pol_hot = l2_policy(1);
     const uint64_t pol_s = l2_policy((p.hints & 2) ? 2 : 0);
@@ -402,9 +404,12 @@ spmm_hop_peers_kernel(const HopDev p, const int64_t n_tiles)
     float *stage_w = stage_all + (size_t)wic * 2 * RT * stride;
     const int64_t per_slab = p.n_long_items + p.n_rows;
 
-    int iter = 0;
 #pragma unroll 1
-    for (int64_t tile = warp; tile < n_tiles; tile += n_warps, ++iter) {
+    for (int iter = 0;; ++iter) {
+        unsigned long long ticket = 0;
+        if (lane == 0) ticket = atomicAdd(p.tile_counter, 1ull);
+        const int64_t tile = (int64_t)__shfl_sync(0xffffffffu, ticket, 0);
+        if (tile >= n_tiles) break;
         float *buf = stage_w + (size_t)(iter & 1) * RT * stride;
         if (bulk) {
             asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
