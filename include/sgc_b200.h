@@ -204,8 +204,8 @@ typedef struct sgc_plan sgc_plan_t;
 size_t  sgc_spmm_plan_workspace_bytes(int64_t n_rows, int64_t nnz, int32_t chunk);
 /* Builds the split table on `stream`; SYNCHRONISES the stream once to read back the item count.
  * The plan keeps pointers into ws_d and to row_ptr_d/col_d: they must outlive the plan.  The first 256 bytes
- * of ws_d are the ticket counter of the multi-GPU hop (K5), reset on the hop's stream before each launch:
- * a plan serves ONE hop with peers at a time (hops on different streams need their own plans). */
+ * of ws_d hold the ticket counters of the persistent hop grids (zeroed here; every launch leaves them zero):
+ * a plan serves ONE hop at a time -- hops that may run concurrently on different streams need their own plans. */
 int32_t sgc_spmm_plan_create(int64_t n_rows, int64_t n_cols, int64_t nnz,
                              const int64_t *row_ptr_d, const int32_t *col_d, int32_t chunk,
                              void *ws_d, size_t ws_bytes, sgc_plan_t **plan_out, void *stream);
@@ -260,15 +260,18 @@ typedef struct sgc_hop_args {
                                   but skip the pushes (results on peers are then stale), bit4 push
                                   with per-lane stores instead of cp.async.bulk, bit5 never merge the
                                   rows of a tile into one bulk store, bit6 end the kernel after the
-                                  source reads of the bulk stores instead of their completion    */
+                                  source reads of the bulk stores instead of their completion;
+                                  bit7: one warp per task in a one-shot grid instead of the persistent,
+                                  ticket-scheduled grid (A/B measurements)                        */
     /* Row-sharded multi-GPU hop (K5): every output row is ALSO stored, from the registers of the
      * SpMM epilogue, to the same (row, column) offset of n_peers other buffers -- the peers'
      * copies of the gathered operand of the next hop, mapped into this process with
      * sgc_ipc_open() and reached over NVLink.  peer_y_d[p] corresponds to y_d (same logical row
      * 0, same leading dimension ldy).  n_peers = 0 for a single-GPU hop. */
     int32_t       n_peers;
-    int32_t       push_tile_tasks; /* consecutive tasks per group slot whose rows travel as one bulk store
-                                      when they are contiguous in y (0 = default 8; rows per tile <= 32)  */
+    int32_t       push_tile_tasks; /* consecutive tasks per group slot a warp draws per ticket (0 = default: 8
+                                      with peers, else 2-4); with peers their rows travel as ONE bulk store
+                                      when they are contiguous in y; rows per tile <= 32                  */
     float        *peer_y_d[SGC_MAX_PEERS];
     /* Optional halo mask, one uint32 per row of this hop (n_rows entries): bit p set = peer p's
      * shard gathers this row in the next hop, so it must be pushed to peer_y_d[p]; clear = peer p

@@ -263,7 +263,12 @@ static int32_t run_hop(const sgc_plan_impl *pl, const sgc_hop_args_t *a, const f
         SGC_REQUIRE(y_vec != 4 || (reinterpret_cast<uintptr_t>(a->peer_y_d[i]) & 15) == 0,
                     "spmm_hop: peer_y_d[%d] must be 16-byte aligned like y_d", i);
     }
-    if (p.n_peers > 0) {
+    // ticket-scheduled persistent grid unless the plan has no counters or the caller asks for the one-shot grid
+    // (hints bit 7, A/B measurements)
+    p.tile_counter = (a->hints & 128) ? nullptr : pl->tile_counter;
+    p.tpw = a->push_tile_tasks > 0 ? a->push_tile_tasks : (p.n_slabs > 1 ? 2 : 4);
+    if (p.tpw * (32 / g) > 32) p.tpw = g;                  // at most 32 tasks per ticket
+    if (peers_on) {
         SGC_REQUIRE(y_vec != 4 || a->f % 4 == 0 || pad_owned,
                     "spmm_hop: peer pushes of a width that is not a multiple of 4 floats need SGC_HOP_PAD_OWNED "
                     "(the bulk stores cover the pad columns)");
@@ -276,8 +281,6 @@ static int32_t run_hop(const sgc_plan_impl *pl, const sgc_hop_args_t *a, const f
         p.stage_stride = (p.n_slabs == 1 && ldy <= slab && y_vec == 4) ? (int32_t)ldy : slab;
         SGC_REQUIRE(pl->tile_counter != nullptr, "spmm_hop: the plan has no workspace (needed by the peer variant)");
         p.tile_counter = pl->tile_counter;
-        // one plan = one hop in flight: the counter is reset on the hop's own stream right before its launch
-        SGC_CUDA_TRY(cudaMemsetAsync(p.tile_counter, 0, sizeof(unsigned long long), s));
     }
     const int64_t n_tasks = (int64_t)p.n_slabs * (p.n_long_items + p.n_rows);
     int32_t rc = fn(p, n_tasks, s);
@@ -365,6 +368,10 @@ int32_t sgc_spmm_plan_create(int64_t n_rows, int64_t n_cols, int64_t nnz,
     P.n_rows = n_rows; P.n_cols = n_cols; P.nnz = nnz;
     P.row_ptr = row_ptr_d; P.col = col_d; P.chunk = chunk;
     P.tile_counter = has_counter ? reinterpret_cast<unsigned long long *>(ws_d) : nullptr;
+    if (has_counter) {
+        cudaError_t e0 = cudaMemsetAsync(ws_d, 0, 256, s);
+        if (e0 != cudaSuccess) { delete pl; return cuda_fail(e0, "plan counters", __FILE__, __LINE__); }
+    }
     if (chunk > 0 && n_rows > 0) {
         char *ws = reinterpret_cast<char *>(ws_d);
         int64_t *n_chunks = reinterpret_cast<int64_t *>(ws + L.off_chunks);

@@ -91,11 +91,11 @@ def _hop_args(g, plan, x, ldx, y, ldy, f, partial, mean, std, std_mode, slab, hi
         if len(peers) > _ffi.MAX_PEERS:
             raise ValueError("at most %d peers" % _ffi.MAX_PEERS)
         a.n_peers = len(peers)
-        a.push_tile_tasks = push_tile_tasks()
         for i, ptr in enumerate(peers):
             a.peer_y_d[i] = int(ptr)
         if peer_mask is not None:
             a.peer_mask_d = _ffi.ptr(peer_mask)
+    a.push_tile_tasks = push_tile_tasks()
     flags = _ffi.HOP_PAD_OWNED if pad_owned else 0
     if use_fused:
         flags |= _ffi.HOP_FUSED_NORM

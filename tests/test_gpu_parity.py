@@ -465,3 +465,62 @@ def test_full_size_reddit_shape_properties(dev):
     assert torch.equal(yk, y2) and secs > 0
     yi, _ = sgc_b200.sgc_precompute(feats, graph, 2)                    # in-place standardisation (default)
     assert torch.equal(yi, y2)
+
+
+@pytest.mark.parametrize("name", ["reddit", "products"])
+def test_full_size_normalisation_vs_oracle(dev, name):
+    """K1 + K2 at BASELINE size (Reddit shape: 23.4 M stored entries with 16 k-entry hub rows through the
+    element-parallel tile / binary-search scheme of csr_fast.cu; products shape: 126 M): row_ptr, col and the
+    fp32 values of S bit for bit against the NumPy restatement of normalization.py:5-12 + utils.py:25, the
+    fp64 values and D^-1/2 within the ulp bar of the golden-vector tests."""
+    import hashlib
+    import sgc_b200
+    from sgc_b200 import synth
+    from oracle import normalization_oracle as no
+    s = synth.make_shape(name, device=dev, with_features=False)
+    n = s["n"]
+    graph = sgc_b200.normalize_csr(n, s["row_ptr"], s["col"], s["val"])
+    ref = no.aug_normalized_adjacency_oracle(n, s["row_ptr"].cpu().numpy(), s["col"].cpu().numpy(),
+                                             s["val"].cpu().numpy())
+    sha = lambda a: hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+    assert graph.nnz == ref["indices"].size > (20_000_000 if name == "reddit" else 120_000_000)
+    assert sha(graph.row_ptr.cpu().numpy()) == sha(ref["indptr"])
+    assert sha(graph.col.cpu().numpy()) == sha(ref["indices"].astype(np.int32))
+    assert sha(graph.values32().cpu().numpy()) == sha(ref["data"].astype(np.float32))
+    d = graph.dinv.cpu().numpy()
+    assert np.max(np.abs(d - ref["d"]) / np.spacing(ref["d"])) <= 1.0          # numpy's pow is within 1 ulp itself
+    v64 = graph.values64().cpu().numpy()
+    assert np.max(np.abs(v64 - ref["data"]) / np.spacing(ref["data"])) <= 4.0
+
+
+def test_full_size_products_shape_hops(dev):
+    """BASELINE configs[3] at full size on one GPU (2.45 M nodes, 126 M stored entries, F = 100, K = 3): the
+    path that runs there -- whole-row kernel <32,4,1> with hot-column tags, long rows split -- against the C
+    oracle on 1500 sampled rows of hop 1 and of hop 3, within north_star's tolerance; tags on/off and the K-hop
+    entry point vs hop by hop bit-identical."""
+    import sgc_b200
+    from sgc_b200 import synth
+    from oracle import spmm_oracle as so
+    s = synth.make_shape("products", device=dev)
+    n, f, k = s["n"], s["f"], s["k"]
+    graph = sgc_b200.normalize_csr(n, s["row_ptr"], s["col"], s["val"])
+    x = sgc_b200.to_padded(s["x"])
+    y1 = sgc_b200.hop(graph, x)
+    plan = graph.plan(sgc_b200.propagate.default_chunk())
+    assert plan.n_hot > 0 and plan.col_tagged is not None              # the tagged variant is what ran
+    assert torch.equal(sgc_b200.hop(graph, x, hints=3), y1)            # tags off: same bits
+    y2 = sgc_b200.hop(graph, y1)
+    y3 = sgc_b200.hop(graph, y2)
+    yk, _ = sgc_b200.sgc_precompute(x, graph, k)
+    assert torch.equal(yk, y3)
+    rng = np.random.RandomState(1)
+    deg = (graph.row_ptr[1:] - graph.row_ptr[:-1]).cpu().numpy()
+    pick = np.unique(np.concatenate([rng.choice(n, 1480, replace=False), np.argsort(deg)[-20:]]))   # + the hubs
+    rp = graph.row_ptr.cpu().numpy()
+    col, val = graph.col.cpu().numpy(), graph.values32().cpu().numpy()
+    sub_ptr = np.zeros(pick.size + 1, dtype=np.int64)
+    np.cumsum(rp[pick + 1] - rp[pick], out=sub_ptr[1:])
+    take = np.concatenate([np.arange(rp[i], rp[i + 1]) for i in pick])
+    for src, dst in ((x, y1), (y2, y3)):
+        want = so.spmm_hop(sub_ptr, col[take], val[take], np.ascontiguousarray(src.cpu().numpy()))
+        assert np.allclose(dst.cpu().numpy()[pick], want, rtol=RTOL, atol=ATOL)
