@@ -282,6 +282,14 @@ typedef struct sgc_hop_args {
 /* One hop Y = S X on `stream`. */
 int32_t sgc_spmm_hop(const sgc_plan_t *plan, const sgc_hop_args_t *args, void *stream);
 
+/* EXPERIMENT, not used by any product path (tools/sweep_tma_gather.py): the plain hop
+ * (sval_d weights, 128-float slabs, 16-byte aligned padded operands) with the gathers of X staged through
+ * shared memory by the TMA unit -- one cp.async.bulk global -> shared per neighbour row piece, `depth` (1..3)
+ * batches of 8 pieces in flight per warp -- instead of per-lane vector loads.  Chunk items of split rows are
+ * left as partial sums (no fix-up pass): timing aid; check results on a chunk = 0 plan. */
+int32_t sgc_exp_spmm_hop_bulk_gather(const sgc_plan_t *plan, const sgc_hop_args_t *args, int32_t depth,
+                                     int32_t ctas_per_sm, void *stream);
+
 /* K hops (utils.py:94-95).  Hop k reads the output of hop k-1; intermediates ping-pong between
  * buf_a_d and buf_b_d ([n, ld_buf] each; needed only when k_hops > 1 / > 2); the last hop writes
  * args->y_d.  The standardisation flags apply to the first hop only.  Square matrices only. */

@@ -266,7 +266,9 @@ static int32_t run_hop(const sgc_plan_impl *pl, const sgc_hop_args_t *a, const f
     // ticket-scheduled persistent grid unless the plan has no counters or the caller asks for the one-shot grid
     // (hints bit 7, A/B measurements)
     p.tile_counter = (a->hints & 128) ? nullptr : pl->tile_counter;
-    p.tpw = a->push_tile_tasks > 0 ? a->push_tile_tasks : (p.n_slabs > 1 ? 2 : 4);
+    // tasks per ticket, measured on B200 (profiles/r02_sweep_persistent.log): Reddit shape (5 slabs) 3.89 ms with
+    // 1, 4.05 with 2, 4.26 with 4; products shape (whole rows) 7.51 / 7.39 / 7.38 ms
+    p.tpw = a->push_tile_tasks > 0 ? a->push_tile_tasks : (p.n_slabs > 1 ? 1 : 4);
     if (p.tpw * (32 / g) > 32) p.tpw = g;                  // at most 32 tasks per ticket
     if (peers_on) {
         SGC_REQUIRE(y_vec != 4 || a->f % 4 == 0 || pad_owned,
@@ -332,8 +334,6 @@ static int32_t run_hop_auto(const sgc_plan_impl *pl, const sgc_hop_args_t *a, co
 }  // namespace sgc
 
 using namespace sgc;
-
-struct sgc_plan { sgc_plan_impl impl; };
 
 extern "C" {
 

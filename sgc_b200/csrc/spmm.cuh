@@ -80,6 +80,12 @@ struct sgc_plan_impl {
     int32_t hot_threshold;
 };
 
+}  // namespace sgc
+
+struct sgc_plan { sgc::sgc_plan_impl impl; };     // the opaque sgc_plan_t of the C ABI
+
+namespace sgc {
+
 typedef int32_t (*hop_launch_fn)(const HopDev &, int64_t n_tasks, cudaStream_t);
 
 // Filled by the instantiation units (spmm_inst_*.cu).
@@ -587,17 +593,20 @@ int32_t launch_hop(const HopDev &p, int64_t n_tasks, cudaStream_t s)
         return SGC_OK;
     } else {
         if (p.tile_counter != nullptr) {
-            const int RT = p.tpw * GPW;
-            const int64_t n_tiles = ceil_div(n_tasks, RT);
-            if (n_tiles <= 0) return SGC_OK;
             auto kern = spmm_hop_ticket_kernel<G, VEC, U, FUSED, STD, HOT>;
             static int occ = 0;                         // per instantiation; the device type is fixed (sm_100a)
             if (occ == 0) SGC_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, HOP_THREADS, 0));
-            const int64_t want = ceil_div(n_tiles, HOP_THREADS / 32);
             const int64_t cap = (int64_t)sm_count() * (occ > 0 ? occ : 1);
-            kern<<<(unsigned)(want < cap ? want : cap), HOP_THREADS, 0, s>>>(p, n_tiles);
-            SGC_LAUNCH_CHECK();
-            return SGC_OK;
+            // small problems (Cora, Pubmed: a few tasks per resident warp) are launch-bound and have no tail to
+            // speak of: one warp per task in a one-shot grid (Pubmed K=2: 0.092 ms vs 0.129 ms with tickets)
+            if (n_tasks > 32 * cap * (HOP_THREADS / 32) * GPW) {
+                const int RT = p.tpw * GPW;
+                const int64_t n_tiles = ceil_div(n_tasks, RT);
+                const int64_t want = ceil_div(n_tiles, HOP_THREADS / 32);
+                kern<<<(unsigned)(want < cap ? want : cap), HOP_THREADS, 0, s>>>(p, n_tiles);
+                SGC_LAUNCH_CHECK();
+                return SGC_OK;
+            }
         }
         const int64_t warps = ceil_div(n_tasks, GPW);
         const int64_t blocks = ceil_div(warps, HOP_THREADS / 32);
