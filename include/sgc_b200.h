@@ -60,7 +60,8 @@ int32_t sgc_l2_set_persisting_bytes(int64_t bytes, int64_t *granted_out);
 /* Measurement aid (bench.py `roofline.l2`, tools/l2_peak.py): reads the `bytes` (multiple of 512) at buf_d
  * `reps` times from all SMs in 512-byte pieces (32 lanes x 16 bytes, the hop kernel's gather shape) with L1
  * allocation off -- with a buffer that stays resident in the 126 MB L2 the CUDA-event time of this launch is
- * the L2 -> SM read bandwidth of the box.  pattern 0: pieces in address order, 1: hashed order (the gather's).
+ * the L2 -> SM read bandwidth of the box.  pattern bit 0: pieces in address order / hashed order (the gather's);
+ * bit 1: L1::no_allocate loads / the hop kernel's own load flavour (L1-allocating, L2 evict_last hint).
  * piece_stride_bytes: distance between pieces (0 = 512, contiguous; 2432 = one 128-float slab of 608-float rows:
  * the Reddit-shaped hop's footprint -- bytes then spans the strided range, of which 512/stride is read).  sink_d: one
  * float the kernel may write (keeps the loads alive).  No counterpart in the reference. */

@@ -20,7 +20,16 @@ __device__ __forceinline__ float4 ld_l2_v4(const float4 *p)
     return r;
 }
 
-// pattern 0: pieces in address order (grid-stride); pattern 1: pieces in a hashed order (the gather's).
+__device__ __forceinline__ float4 ld_hint_v4(const float4 *p, uint64_t pol)
+{
+    float4 r;
+    asm volatile("ld.global.nc.L2::cache_hint.v4.f32 {%0,%1,%2,%3}, [%4], %5;"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p), "l"(pol));
+    return r;
+}
+
+// pattern bit 0: 0 = pieces in address order (grid-stride), 1 = pieces in a hashed order (the gather's);
+// pattern bit 1: 0 = L1::no_allocate loads, 1 = the hop kernel's own load (L1-allocating, L2 evict_last hint).
 __global__ void __launch_bounds__(PROBE_THREADS)
 l2_read_probe_kernel(const float4 *__restrict__ buf, int64_t n_pieces, int64_t stride_v4, int32_t reps,
                      int32_t pattern, float *__restrict__ sink)
@@ -29,6 +38,9 @@ l2_read_probe_kernel(const float4 *__restrict__ buf, int64_t n_pieces, int64_t s
     const int64_t warp = (int64_t)blockIdx.x * (PROBE_THREADS / 32) + (threadIdx.x >> 5);
     const int64_t n_warps = (int64_t)gridDim.x * (PROBE_THREADS / 32);
     float acc = 0.f;
+    uint64_t pol;
+    asm("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+    const bool hashed = (pattern & 1) != 0, alloc = (pattern & 2) != 0;
     for (int r = 0; r < reps; ++r) {
         for (int64_t p0 = warp; p0 < n_pieces; p0 += n_warps * PROBE_UNROLL) {
             float4 v[PROBE_UNROLL];
@@ -36,12 +48,12 @@ l2_read_probe_kernel(const float4 *__restrict__ buf, int64_t n_pieces, int64_t s
             for (int u = 0; u < PROBE_UNROLL; ++u) {
                 int64_t p = p0 + (int64_t)u * n_warps;
                 if (p >= n_pieces) p = warp;
-                if (pattern == 1) {
+                if (hashed) {
                     uint64_t z = (uint64_t)p * 0x9E3779B97F4A7C15ull + (uint64_t)r * 0xD1B54A32D192ED03ull;
                     z ^= z >> 29;
                     p = (int64_t)(((z >> 32) * (uint64_t)n_pieces) >> 32);      // n_pieces < 2^32
                 }
-                v[u] = ld_l2_v4(buf + p * stride_v4 + lane);
+                v[u] = alloc ? ld_hint_v4(buf + p * stride_v4 + lane, pol) : ld_l2_v4(buf + p * stride_v4 + lane);
             }
 #pragma unroll
             for (int u = 0; u < PROBE_UNROLL; ++u) acc += v[u].x + v[u].y + v[u].z + v[u].w;
@@ -64,7 +76,7 @@ int32_t sgc_l2_read_probe(const void *buf_d, int64_t bytes, int64_t piece_stride
     SGC_REQUIRE(buf_d && sink_d, "l2_read_probe: null pointer");
     SGC_REQUIRE((reinterpret_cast<uintptr_t>(buf_d) & 15) == 0 && bytes >= 512,
                 "l2_read_probe: buffer must be 16-byte aligned and hold at least one 512-byte piece");
-    SGC_REQUIRE(reps >= 1 && (pattern == 0 || pattern == 1), "l2_read_probe: bad reps / pattern");
+    SGC_REQUIRE(reps >= 1 && pattern >= 0 && pattern <= 3, "l2_read_probe: bad reps / pattern");
     if (ctas_per_sm < 1) ctas_per_sm = 8;
     const int grid = sm_count() * ctas_per_sm;
     l2_read_probe_kernel<<<grid, PROBE_THREADS, 0, as_stream(stream)>>>(

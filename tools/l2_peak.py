@@ -20,7 +20,7 @@ print("%8s %8s %6s %10s %10s" % ("MB", "order", "CTAs", "ms", "GB/s"))
 for mb in (8, 16, 32, 48, 64, 96, 128, 256, 1024):
     buf = torch.ones(mb * 1024 * 1024 // 4, dtype=torch.float32, device=dev)
     reps = max(2, 2048 // mb)
-    for pattern in (0, 1):
+    for pattern in (0, 1, 2, 3):
         for ctas in (4, 8):
             call = lambda: _ffi.call("sgc_l2_read_probe", buf.data_ptr(), buf.numel() * 4, 0, reps, pattern, ctas,
                                      sink.data_ptr(), torch.cuda.current_stream().cuda_stream)
@@ -33,15 +33,15 @@ for mb in (8, 16, 32, 48, 64, 96, 128, 256, 1024):
                 torch.cuda.synchronize()
                 ts.append(a.elapsed_time(b))
             ms = min(ts)
-            print("%8d %8s %6d %10.3f %10.0f" % (mb, "address" if pattern == 0 else "hashed", ctas, ms,
-                                                 mb * 1024 * 1024 * reps / (ms * 1e-3) / 1e9), flush=True)
+            print("%8d %8s %6d %10.3f %10.0f" % (mb, ("hashed" if pattern & 1 else "address") + ("+hint" if pattern & 2 else ""),
+                                                 ctas, ms, mb * 1024 * 1024 * reps / (ms * 1e-3) / 1e9), flush=True)
     del buf
 
 # the Reddit-shaped hop's footprint: 512-byte pieces (one 128-float slab) of 232,965 rows at a 2432-byte pitch
 n, pitch = 232965, 2432
 buf = torch.ones(n * pitch // 4, dtype=torch.float32, device=dev)
 print("strided: %d pieces of 512 B at a %d-byte pitch (%.0f MB touched in %.0f MB)" % (n, pitch, n * 512 / 1e6, n * pitch / 1e6))
-for pattern in (0, 1):
+for pattern in (0, 1, 2, 3):
     for ctas in (4, 7, 8):
         reps = 20
         call = lambda: _ffi.call("sgc_l2_read_probe", buf.data_ptr(), buf.numel() * 4, pitch, reps, pattern, ctas,
@@ -55,5 +55,5 @@ for pattern in (0, 1):
             torch.cuda.synchronize()
             ts.append(a.elapsed_time(b))
         ms = min(ts)
-        print("%8s %8s %6d %10.3f %10.0f" % ("slab", "address" if pattern == 0 else "hashed", ctas, ms,
+        print("%8s %8s %6d %10.3f %10.0f" % ("slab", ("hashed" if pattern & 1 else "address") + ("+hint" if pattern & 2 else ""), ctas, ms,
                                              n * 512 * reps / (ms * 1e-3) / 1e9), flush=True)
