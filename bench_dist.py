@@ -95,8 +95,9 @@ def _timed_steps(args, dev, B, step, before_step=None):
 
 
 # --------------------------------------------------------------------------------------------------
-def run_feature_sharded(name, args, rank, world, dev, B, lam=0.0, with_e2e=True):
-    """S replicated, X split by columns; no exchange.  Checked against rank 0's single-GPU result."""
+def run_feature_sharded(name, args, rank, world, dev, B, lam=0.0, with_e2e=True, e2e_only=False):
+    """S replicated, X split by columns; no exchange.  Checked against rank 0's single-GPU result.
+    e2e_only: just the host-to-host figure of this sharding (the device-timed leg ran on another grid)."""
     synth = B["load_synth"]()
     from sgc_b200.features import col_stats, standardize_, to_padded
     from sgc_b200.graph import normalize_csr
@@ -107,6 +108,18 @@ def run_feature_sharded(name, args, rank, world, dev, B, lam=0.0, with_e2e=True)
     s = synth.make_shape(name, device=dev, with_features=False, lam=lam)
     x = synth.gaussian_features(n, f, seed=1, scaled=shape["scaled"], device=dev)
     x_raw_local = x[:, c0:c1].contiguous()
+    if e2e_only:
+        del x
+        torch.cuda.empty_cache()
+        nnz = int(s["col"].numel()) + n          # A has no self-loops: S = A + I stores nnz(A) + N entries
+        e2e = None
+        if c1 > c0:
+            e2e = _feature_sharded_e2e(args, s, x_raw_local, shape, n, f, k, nnz, c0, c1, world, dev, B)
+        else:
+            dist.barrier(); dist.barrier()
+            z = torch.zeros(1, dtype=torch.float64, device=dev); dist.all_reduce(z, op=dist.ReduceOp.MAX)
+            z = torch.zeros(1, dtype=torch.int64, device=dev); dist.all_reduce(z)
+        return {"e2e": e2e}
     if shape["scaled"]:
         mean, std = col_stats(x)
         standardize_(x, mean, std)
@@ -192,16 +205,18 @@ def _feature_sharded_e2e(args, s, x_raw_local, shape, n, f, k, nnz, c0, c1, worl
 
 
 # --------------------------------------------------------------------------------------------------
-def _workload_inputs(name, rank, world, dev, lam, want_single, B):
+def _workload_inputs(name, rank, world, dev, lam, want_single, B, grid=None):
     """This rank's rows of the named synthetic workload: raw CSR slice (global column ids) and the
     feature rows the hops start from (Reddit shape: standardised as utils.py:119 does, with the
-    statistics of ALL rows).  Rank 0 also runs the whole workload on its one GPU (timing + result)."""
+    statistics of ALL rows); on a grid (dist.Grid) the rows of this rank's row part and the columns of its
+    column block.  Rank 0 also runs the whole workload on its one GPU (timing + result)."""
     synth = B["load_synth"]()
     from sgc_b200.features import col_stats, standardize_
     shape = synth.SHAPES[name]
     n, f, k = shape["n"], shape["f"], shape["k"]
-    n_pad, parts = sd.partition_rows(n, world)
-    row0, row1 = parts[rank]
+    part_rank, part_world = (grid.ri, grid.p_rows) if grid is not None else (rank, world)
+    n_pad, parts = sd.partition_rows(n, part_world)
+    row0, row1 = parts[part_rank]
     single = y_single = None
     if shape["symmetric"]:
         s = synth.make_shape(name, device=dev, with_features=False, lam=lam)     # every rank builds the graph, keeps its rows
@@ -224,6 +239,8 @@ def _workload_inputs(name, rank, world, dev, lam, want_single, B):
         rp, col, val = s["row_ptr"], s["col"], s["val"]
         x_local = synth.gaussian_features(n, f, seed=1, scaled=False, row_range=(row0, row1), device=dev)
         del s
+    if grid is not None and grid.p_cols > 1:
+        x_local = x_local[:, grid.cols[0]:grid.cols[1]].contiguous()
     torch.cuda.empty_cache()
     return n, f, k, n_pad, rp, col, val, x_local, single, y_single
 
@@ -271,20 +288,24 @@ def _push_breakdown(prop, k_hops, dev, reps=5):
     return res
 
 
-def run_row_sharded(name, args, rank, world, dev, B, lam=0.0, with_e2e=True, want_single=True, steps=None):
+def run_row_sharded(name, args, rank, world, dev, B, lam=0.0, with_e2e=True, want_single=True, steps=None, grid=None):
     """Times K-hop row-sharded propagation of one named workload on `world` GPUs (strong scaling: the
-    graph is fixed, rows are split over the ranks), then checks the result (dist.verify_sharded)."""
+    graph is fixed, rows are split over the ranks), then checks the result (dist.verify_sharded).  With a
+    dist.Grid of more than one column block, every row group (the ranks sharing a column block) runs the
+    row-sharded propagation on its block: rows are split over grid.p_rows ranks only."""
     from sgc_b200.propagate import default_chunk
-    n, f, k, n_pad, rp, col, val, x_local, single, y_single = _workload_inputs(name, rank, world, dev, lam, want_single, B)
+    n, f, k, n_pad, rp, col, val, x_local, single, y_single = _workload_inputs(name, rank, world, dev, lam, want_single, B, grid)
+    group = grid.row_group if grid is not None else None
+    c0, c1 = grid.cols if grid is not None else (0, f)
     torch.cuda.synchronize()
     t0 = time.perf_counter()
-    sg = sd.shard_normalize(n, rp, col, val)
+    sg = sd.shard_normalize(n, rp, col, val, group=group)
     torch.cuda.synchronize()
     normalise_ms = (time.perf_counter() - t0) * 1e3
     nnz_local = torch.tensor([sg.graph.nnz], dtype=torch.int64, device=dev)
-    dist.all_reduce(nnz_local)
+    dist.all_reduce(nnz_local, group=group)
     nnz = int(nnz_local.item())
-    prop = sd.ShardedPropagator(sg, f)
+    prop = sd.ShardedPropagator(sg, c1 - c0, group=group)
     mode = prop.mode
     for blk in prop.blocks:
         if blk is not None:
@@ -303,8 +324,23 @@ def run_row_sharded(name, args, rank, world, dev, B, lam=0.0, with_e2e=True, wan
            "push_fraction": getattr(prop, "push_fraction", 1.0),
            "n_blocks": prop.n_blocks, "normalise_ms": normalise_ms, "ms_per_step": ms_per_step,
            "value": k * nnz * f / (ms_per_step * 1e-3), "launches": launches, "clocks": clocks,
-           "single": single, "e2e": None, "steps": a2.steps}
-    out["parity"] = sd.verify_sharded(prop, x_local, k, B, y_single=y_single) if mode == "push" else None
+           "single": single, "e2e": None, "steps": a2.steps,
+           "grid": [grid.p_cols, grid.p_rows] if grid is not None else [1, world], "cols_per_rank": c1 - c0}
+    if mode != "push":
+        out["parity"] = None
+    elif grid is None or grid.p_cols == 1:
+        out["parity"] = sd.verify_sharded(prop, x_local, k, B, y_single=y_single)
+    else:
+        # inside the row group: pushed rows owner-vs-copy and sampled rows against the reference's torch.spmm;
+        # over all ranks: every rank's [rows, columns] block against the single-GPU result, bit for bit
+        rep = sd.verify_sharded(prop, x_local, k, B, y_single=None, group=group)
+        y_local = prop.buf[k % 2][sg.row0:sg.row1, :c1 - c0]
+        rep["vs_single_gpu"] = sd.verify_against_single(y_local, y_single, sg.row0, c0, f)
+        ok = torch.tensor([1 if (rep["ok"] and rep["vs_single_gpu"]["ok"]) else 0], dtype=torch.int64, device=dev)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        rep["ok"] = bool(int(ok.item()))
+        rep["scope"] = "hop-by-hop figures are those of rank 0's row group; ok and vs_single_gpu cover all ranks"
+        out["parity"] = rep
     del y_single
     out["breakdown"] = _push_breakdown(prop, k, dev)
     if with_e2e:
@@ -349,12 +385,26 @@ def _row_sharded_e2e(args, prop, sg, rp, col, val, x_local, n, f, k, nnz, mode, 
 
 
 def run_workload(name, args, rank, world, dev, B, lam=0.0, with_e2e=True, want_single=True, steps=None):
+    """One leg: the device-timed K hops on the grid dist.choose_grid picks (column blocks x row parts), its
+    result check, and -- when asked -- the host-to-host figure: through the pipelined feature-sharded host path
+    wherever the shape allows feature sharding (dist.choose_sharding; PCIe-bound, the hops are a tenth of it),
+    else through the row-sharded one."""
     synth = B["load_synth"]()
     shape = synth.SHAPES[name]
     approx_nnz = shape["pairs"] * (2 if shape["symmetric"] else 1) + shape["n"]
-    if sd.choose_sharding(shape["n"], approx_nnz, shape["f"], world) == "features":
+    p_cols, p_rows = sd.choose_grid(shape["n"], approx_nnz, shape["f"], shape["k"], world)
+    feature_e2e = sd.choose_sharding(shape["n"], approx_nnz, shape["f"], world) == "features"
+    if p_rows == 1:
         return run_feature_sharded(name, args, rank, world, dev, B, lam, with_e2e)
-    return run_row_sharded(name, args, rank, world, dev, B, lam, with_e2e, want_single, steps)
+    grid = sd.make_grid(shape["f"], p_cols, p_rows) if p_cols > 1 else None
+    r = run_row_sharded(name, args, rank, world, dev, B, lam, with_e2e and not feature_e2e, want_single, steps, grid)
+    if with_e2e and feature_e2e:
+        r["e2e"] = run_feature_sharded(name, args, rank, world, dev, B, lam, True, e2e_only=True)["e2e"]
+        if r["e2e"] is not None:
+            r["e2e"]["value"] = shape["k"] * r["nnz"] * shape["f"] / (r["e2e"]["ms_per_step"] * 1e-3)
+            r["e2e"]["sharding"] = "feature-sharded x%d host pipeline (the device-timed value above uses the %dx%d grid)" \
+                                   % (world, p_cols, p_rows)
+    return r
 
 
 def parallelism_text(r, world):
@@ -362,6 +412,15 @@ def parallelism_text(r, world):
         return ("feature-sharded x%d: S replicated on every GPU, X split into contiguous column blocks of <= %d "
                 "columns; column c of S^K X depends on column c of X only, so the K hops (and the per-column "
                 "standardisation) need no exchange; output column-sharded" % (world, r.get("cols_per_rank", 0)))
+    if r["mode"] == "push" and r.get("grid", [1, world])[0] > 1:
+        pc, pr = r["grid"]
+        return ("grid-sharded %d column blocks x %d row parts: the %d GPUs that share a column block (<= %d columns) "
+                "split the rows of S among them and run the row-sharded hop on that block -- exchange fused into the "
+                "SpMM kernel (output rows staged in shared memory, cp.async.bulk to the %d peers' next-hop operands "
+                "over NVLink, CUDA-IPC mapped), one 1-element all-reduce inside the row group as barrier per hop; "
+                "%.1f%% of rows x peers pushed; column blocks never communicate (column c of S^K X depends on column "
+                "c of X only); output sharded by rows and columns"
+                % (pc, pr, pr, r.get("cols_per_rank", 0), pr - 1, 100.0 * r["push_fraction"]))
     if r["mode"] == "push":
         return ("row-sharded x%d; exchange fused into the SpMM kernel: output rows are staged in shared memory and "
                 "written by cp.async.bulk (tiles of consecutive rows) to all peers' next-hop operands over NVLink "
@@ -398,7 +457,8 @@ def bench(args, rank, world, dev, B):
     name = args.workload
     failed = []
     r = run_workload(name, args, rank, world, dev, B, lam=0.0,
-                     with_e2e=(name != "papers100m" or os.environ.get("SGC_BENCH_PAPERS_E2E") == "1"),
+                     with_e2e=(not getattr(args, "skip_e2e", False))
+                     and (name != "papers100m" or os.environ.get("SGC_BENCH_PAPERS_E2E") == "1"),
                      want_single=(name != "papers100m"))
     if r["parity"] is not None and not r["parity"]["ok"]:
         failed.append(name)
@@ -443,7 +503,7 @@ def bench(args, rank, world, dev, B):
             "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": B["workload_config"](name, n, nnz, f, k),
-            "roofline": {"bound": "l2" if r["mode"] == "features" else "hbm", "achieved": achieved, "peak": peak,
+            "roofline": {"bound": "l2" if (r["mode"] == "features" or n * 128 * 4 <= 128 * 1024 * 1024) else "hbm", "achieved": achieved, "peak": peak,
                          "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                          "achieved_is": "gather-model bytes per GPU / step time (multi-GPU kernels are not run under "
                                         "ncu); peak is the measured HBM copy figure -- for the L2-resident Reddit slabs "
@@ -454,6 +514,7 @@ def bench(args, rank, world, dev, B):
                        **{kk: (v.get("parity") or {}).get("ok") for kk, v in extras.items() if isinstance(v, dict) and "parity" in v},
                        "detail": r["parity"]},
             "details": {"parallelism": parallelism_text(r, world), "dist_mode": r["mode"],
+                        "grid_cols_x_rows": r.get("grid", [world, 1]),
                         "normalise_ms": r["normalise_ms"], "partition_locality_lambda": r["lam"],
                         "pushed_rows_x_peers_fraction": r["push_fraction"], "rows_per_rank": r["n_pad"],
                         "per_hop_breakdown": r["breakdown"]},

@@ -313,12 +313,14 @@ class ShardedPropagator(object):
         for q in range(sg.world):
             if q == sg.rank:
                 continue
+            # P2POp takes the peer's GLOBAL rank; q counts inside the group (a row group of a grid)
+            peer = q if self.group is None else dist.get_global_rank(self.group, q)
             if b > a:
-                ops.append(dist.P2POp(dist.isend, dst[sg.row0 + a:sg.row0 + b], q, self.group))
+                ops.append(dist.P2POp(dist.isend, dst[sg.row0 + a:sg.row0 + b], peer, self.group))
             qa, qb = self.block_rows(q, r)
             if qb > qa:
                 base = q * sg.n_pad
-                ops.append(dist.P2POp(dist.irecv, dst[base + qa:base + qb], q, self.group))
+                ops.append(dist.P2POp(dist.irecv, dst[base + qa:base + qb], peer, self.group))
         return dist.batch_isend_irecv(ops) if ops else []
 
     def load(self, x_local):
@@ -574,6 +576,98 @@ def choose_sharding(n, nnz, f, world, mem_bytes=170e9):
     widest = max(c1 - c0 for c0, c1 in partition_features(f, world))
     fits = nnz * 20.0 + n * 8.0 + 3.0 * n * _pad8(widest) * 4.0 < mem_bytes
     return "features" if (fits and f // world >= 64) else "rows"
+
+
+# --------------------------------------------------------------------------------------------------
+# 2-D ("grid") sharding: P_c column blocks x P_r row parts, world = P_c * P_r.  The P_r ranks that share a
+# column block form a ROW GROUP and run the row-sharded propagation above on that block (exchange fused into
+# the hop, barrier inside the group only); different column blocks never talk to each other.  (P_c, P_r) =
+# (world, 1) is feature sharding, (1, world) is row sharding.  Why both axes: splitting columns costs lane
+# efficiency once a block is narrower than a few 128-float slabs (an 80-column block costs 0.85 ms where 1/8 of
+# 602 columns would cost 0.62 ms, profiles/r01_sweep_block.log), splitting rows costs NVLink egress
+# (rows/P_r x (P_r - 1) row pushes per exchanging hop) that hides behind the gathers only while it is shorter
+# than them.  Reddit shape on 8 GPUs: 2 x 4.
+NVLINK_PUSH_BYTES_PER_MS = 5.5e8          # egress per GPU inside the fused hop (profiles/r02_nvlink_probe_n8_products.log)
+SLAB_PASS_MS_PER_ENTRY = 3.4e-8           # one 128-float slab pass over all stored entries (Reddit shape: 0.8 ms)
+
+
+def _block_cost_slabs(w):
+    """Cost of one hop over a w-column block in units of a full 128-float slab pass (profiles/r01_sweep_block.log:
+    32 columns 0.47, 48-64 0.65, 80-96 0.92, 112-128 1.0; a remainder of at most 64 columns runs as its own
+    launch with narrower lane groups)."""
+    full, r = divmod(int(w), 128)
+    rem = 0.0 if r == 0 else (0.47 if r <= 32 else (0.65 if r <= 64 else (0.92 if r <= 96 else 1.0)))
+    return full + rem
+
+
+def grid_cost_ms(n, nnz, f, k, p_cols, p_rows):
+    """Modelled time of K hops on a p_cols x p_rows grid (relative ranking of the grids; not a prediction)."""
+    w = max(c1 - c0 for c0, c1 in partition_features(f, p_cols))
+    compute = SLAB_PASS_MS_PER_ENTRY * nnz * _block_cost_slabs(w) / p_rows
+    rows = (n + p_rows - 1) // p_rows
+    exchange = rows * _pad8(w) * 4.0 * (p_rows - 1) / NVLINK_PUSH_BYTES_PER_MS
+    barrier = 0.04 if p_rows > 1 else 0.0
+    fused = 1.15 * max(compute, exchange) if p_rows > 1 else compute
+    return (k - 1) * (fused + barrier) + compute + barrier
+
+
+def choose_grid(n, nnz, f, k, world, mem_bytes=170e9):
+    """(p_cols, p_rows) for `world` GPUs.  SGC_B200_GRID=CxR forces a grid, SGC_B200_SHARDING=rows|features the
+    two degenerate ones.  Column splits are considered only where `choose_sharding` would allow them (every
+    block at least 64 columns) and a 128-float slab of the gathered operand stays L2-resident (the regime the
+    cost model was measured in); operands far larger than L2 (products, papers100M) take pure row sharding."""
+    from .graph import L2_SLAB_BUDGET
+    forced = os.environ.get("SGC_B200_GRID")
+    if forced:
+        pc, pr = (int(v) for v in forced.lower().split("x"))
+        if pc * pr != world or pc < 1 or pr < 1:
+            raise ValueError("SGC_B200_GRID=%s does not describe %d GPUs" % (forced, world))
+        return pc, pr
+    forced = os.environ.get("SGC_B200_SHARDING")
+    if forced == "rows":
+        return 1, world
+    if forced == "features":
+        return world, 1
+    best = None
+    for pc in range(1, world + 1):
+        if world % pc:
+            continue
+        pr = world // pc
+        w = max(c1 - c0 for c0, c1 in partition_features(f, pc))
+        if pc > 1 and (f // pc < 64 or n * 128 * 4.0 > L2_SLAB_BUDGET):
+            continue
+        if nnz / pr * 20.0 + n * 8.0 + 3.0 * n * _pad8(w) * 4.0 >= mem_bytes:
+            continue
+        cost = grid_cost_ms(n, nnz, f, k, pc, pr)
+        if best is None or cost < best[0] - 1e-9:
+            best = (cost, pc, pr)
+    if best is None:
+        return 1, world
+    return best[1], best[2]
+
+
+class Grid(object):
+    """This rank's place in a p_cols x p_rows grid: ranks [ci*p_rows, (ci+1)*p_rows) share column block ci."""
+
+    def __init__(self, rank, world, p_cols, p_rows, row_group, cols):
+        self.rank, self.world, self.p_cols, self.p_rows = rank, world, p_cols, p_rows
+        self.ci, self.ri = rank // p_rows, rank % p_rows
+        self.row_group, self.cols = row_group, cols
+
+
+def make_grid(f, p_cols, p_rows):
+    """Collective over the default group: builds the row groups (every rank must take part in the creation
+    of every group, torch.distributed.new_group) and returns this rank's Grid."""
+    rank, world = dist.get_rank(), dist.get_world_size()
+    if p_cols * p_rows != world:
+        raise ValueError("grid %dx%d does not describe %d ranks" % (p_cols, p_rows, world))
+    mine = None
+    for ci in range(p_cols):
+        ranks = list(range(ci * p_rows, (ci + 1) * p_rows))
+        g = dist.group.WORLD if p_cols == 1 else dist.new_group(ranks)
+        if rank in ranks:
+            mine = g
+    return Grid(rank, world, p_cols, p_rows, mine, partition_features(f, p_cols)[rank // p_rows])
 
 
 def propagate_feature_sharded(graph, x_cols, degree, **kw):

@@ -263,3 +263,88 @@ def test_replication_check_finds_a_stale_pushed_row():
         clean, masked, dirty = ret[rank]
         assert clean[0] == 0 and clean[1] > 0 and masked[0] == 0 and 0 < masked[1] <= clean[1]
         assert dirty[0] == 1 and dirty[1] == masked[1]
+
+
+# --------------------------------------------------------------------------------------------------
+# 2-D grid sharding (dist.make_grid / choose_grid): column blocks x row parts
+def grid_worker(rank, world, port, p_cols, p_rows, k, ret):
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from oracle import spmm_oracle as so
+        from sgc_b200 import dist as sd
+        from sgc_b200.graph import SgcGraph
+        indptr, indices, data, x = make_problem(n=61, f=150)
+        n, f = x.shape
+        grid = sd.make_grid(f, p_cols, p_rows)
+        assert (grid.ci, grid.ri) == (rank // p_rows, rank % p_rows)
+        assert dist.get_world_size(grid.row_group) == p_rows and dist.get_rank(grid.row_group) == grid.ri
+        c0, c1 = grid.cols
+        n_pad, parts = sd.partition_rows(n, p_rows)
+        row0, row1 = parts[grid.ri]
+        b, e = indptr[row0], indptr[row1]
+        g = SgcGraph(row1 - row0, p_rows * n_pad, torch.from_numpy(indptr[row0:row1 + 1] - b),
+                     torch.from_numpy(indices[b:e]), None, None, sval=torch.from_numpy(data[b:e]))
+        sg = sd.ShardedGraph(g, grid.ri, p_rows, n, n_pad, row0, row1)
+
+        def cpu_hop(graph, xin, out):
+            rp = graph.row_ptr.numpy()
+            y = so.spmm_hop(rp - rp[0], graph.col.numpy()[rp[0]:rp[-1]], graph.sval.numpy()[rp[0]:rp[-1]],
+                            np.ascontiguousarray(xin.numpy()))
+            out.copy_(torch.from_numpy(y))
+
+        y = sd.propagate_sharded(sg, torch.from_numpy(x[row0:row1, c0:c1].copy()), k, row_blocks=2,
+                                 group=grid.row_group, hop_fn=cpu_hop)
+        # every rank's [rows, columns] block against the single-process result held by rank 0 only
+        want = None
+        if rank == 0:
+            want = torch.from_numpy(so.sgc_precompute_oracle(x, indptr, indices, data, k)[0])
+        rep = sd.verify_against_single(y, want, row0, c0, f)
+        ret[rank] = (row0, row1, c0, c1, y.numpy().copy(), rep["ok"], rep["per_rank"])
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,p_cols,p_rows,k", [(4, 2, 2, 2), (2, 1, 2, 3), (2, 2, 1, 2), (4, 1, 4, 2)])
+def test_grid_sharded_matches_single_process(world, p_cols, p_rows, k):
+    from oracle import spmm_oracle as so
+    indptr, indices, data, x = make_problem(n=61, f=150)
+    want, _ = so.sgc_precompute_oracle(x, indptr, indices, data, k)
+    ret = mp.Manager().dict()
+    mp.spawn(grid_worker, args=(world, free_port(), p_cols, p_rows, k, ret), nprocs=world, join=True)
+    got = np.full_like(want, np.nan)
+    for rank in range(world):
+        row0, row1, c0, c1, y, ok, per_rank = ret[rank]
+        assert ok and all(per_rank), (rank, per_rank)
+        got[row0:row1, c0:c1] = y
+    assert np.array_equal(got, want)             # the blocks tile the whole matrix
+
+
+def test_choose_grid(monkeypatch):
+    from sgc_b200 import dist as sd
+    monkeypatch.delenv("SGC_B200_GRID", raising=False)
+    monkeypatch.delenv("SGC_B200_SHARDING", raising=False)
+    for world in (1, 2, 4, 8):
+        for shape in ((232965, 23.4e6, 602, 2), (2449029, 126e6, 100, 3), (111059956, 1.75e9, 128, 3), (19717, 1.1e5, 500, 2)):
+            pc, pr = sd.choose_grid(*shape, world)
+            assert pc * pr == world and pc >= 1 and pr >= 1
+            if pc > 1:
+                assert shape[2] // pc >= 64                      # blocks stay at least 64 columns wide
+    # operands far larger than L2 and narrow feature matrices: pure row sharding
+    assert sd.choose_grid(2449029, 126e6, 100, 3, 8) == (1, 8)
+    assert sd.choose_grid(111059956, 1.75e9, 128, 3, 8) == (1, 8)
+    # Reddit shape on 8 GPUs: neither 8 narrow column blocks nor 7 peers per row
+    pc, pr = sd.choose_grid(232965, 23.4e6, 602, 2, 8)
+    assert 1 < pc < 8 and 1 < pr < 8
+    monkeypatch.setenv("SGC_B200_GRID", "4x2")
+    assert sd.choose_grid(232965, 23.4e6, 602, 2, 8) == (4, 2)
+    with pytest.raises(ValueError):
+        sd.choose_grid(232965, 23.4e6, 602, 2, 4)
+    monkeypatch.delenv("SGC_B200_GRID")
+    monkeypatch.setenv("SGC_B200_SHARDING", "rows")
+    assert sd.choose_grid(232965, 23.4e6, 602, 2, 8) == (1, 8)
+    monkeypatch.setenv("SGC_B200_SHARDING", "features")
+    assert sd.choose_grid(232965, 23.4e6, 602, 2, 8) == (8, 1)
+    # the cost model: more row parts -> less compute per rank, more egress per exchanging hop
+    assert sd.grid_cost_ms(232965, 23.4e6, 602, 2, 1, 8) < sd.grid_cost_ms(232965, 23.4e6, 602, 2, 1, 2)
+    assert sd.grid_cost_ms(232965, 23.4e6, 602, 1, 2, 4) < sd.grid_cost_ms(232965, 23.4e6, 602, 2, 2, 4)
