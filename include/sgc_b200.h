@@ -290,6 +290,10 @@ int32_t sgc_spmm_hop(const sgc_plan_t *plan, const sgc_hop_args_t *args, void *s
  * left as partial sums (no fix-up pass): timing aid; check results on a chunk = 0 plan. */
 int32_t sgc_exp_spmm_hop_bulk_gather(const sgc_plan_t *plan, const sgc_hop_args_t *args, int32_t depth,
                                      int32_t ctas_per_sm, void *stream);
+/* Same experiment with the tensor form of the TMA gather: cp.async.bulk.tensor.2d ... tile::gather4 over a 2-D
+ * tensor map of X ([rows, ldx] floats, box 128 x 1) -- four neighbour rows per instruction. */
+int32_t sgc_exp_spmm_hop_gather4(const sgc_plan_t *plan, const sgc_hop_args_t *args, int32_t depth,
+                                 int32_t ctas_per_sm, void *stream);
 
 /* K hops (utils.py:94-95).  Hop k reads the output of hop k-1; intermediates ping-pong between
  * buf_a_d and buf_b_d ([n, ld_buf] each; needed only when k_hops > 1 / > 2); the last hop writes

@@ -78,6 +78,7 @@ SIGNATURES = {
     "sgc_spmm_hop": (c_i32, [c_p, ctypes.POINTER(HopArgs), c_p]),
     "sgc_precompute": (c_i32, [c_p, ctypes.POINTER(HopArgs), c_i32, c_p, c_p, c_i64, c_p]),
     "sgc_exp_spmm_hop_bulk_gather": (c_i32, [c_p, ctypes.POINTER(HopArgs), c_i32, c_i32, c_p]),
+    "sgc_exp_spmm_hop_gather4": (c_i32, [c_p, ctypes.POINTER(HopArgs), c_i32, c_i32, c_p]),
     "sgc_sort_workspace_bytes": (c_sz, [c_i64]),
     "sgc_sort_by_key_i32": (c_i32, [c_i64, c_i32, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_sz, c_p]),
     "sgc_csr_expand_rows": (c_i32, [c_i64, c_p, c_i32, c_p, c_p]),

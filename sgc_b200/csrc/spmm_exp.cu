@@ -10,10 +10,13 @@
 // shared memory and accumulate in the same ascending order as the product kernel, so results are bit-identical
 // and the experiment is checked, not just timed.
 //
-// (The tensor form, cp.async.bulk.tensor.2d ... tile::gather4, moves 4 rows per instruction through the same
-// TMA -> L2 path; it additionally needs a CUtensorMap per operand.  The non-tensor bulk copy measures that path
-// without it: what bounds the Reddit-shaped hop is L2 -> SM bandwidth, which B300_MICROARCH.md reports as
-// path-independent between LDG and TMA.)
+// Second form (G4 = true, sgc_exp_spmm_hop_gather4): the tensor instruction cp.async.bulk.tensor.2d ...
+// tile::gather4 -- ONE instruction names four row indices of X (a 2-D CUtensorMap over [rows, ldx], box 128 x 1)
+// and the TMA unit lands the four 512-byte slab pieces in consecutive shared-memory rows: a batch of 8
+// neighbours is 2 instructions instead of 8 bulk copies.  Columns past ldx (the last slab of a 602-column
+// matrix) are zero-filled by the unit.
+#include <cuda.h>
+#include <cstring>
 #include "spmm.cuh"
 
 namespace sgc {
@@ -24,9 +27,9 @@ constexpr int EXP_SW = 128;         // slab width in floats (512-byte pieces)
 
 __device__ __forceinline__ uint32_t exp_smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
-template <int DEPTH>
+template <int DEPTH, bool G4>
 __global__ void __launch_bounds__(EXP_THREADS)
-spmm_hop_bulk_gather_kernel(const HopDev p, const int64_t n_tasks)
+spmm_hop_bulk_gather_kernel(const HopDev p, const int64_t n_tasks, const __grid_constant__ CUtensorMap tmap)
 {
     constexpr int WARPS = EXP_THREADS / 32;
     extern __shared__ __align__(128) float exp_smem[];
@@ -96,7 +99,29 @@ spmm_hop_bulk_gather_kernel(const HopDev p, const int64_t n_tasks)
             int32_t cj[EXP_BATCH];
 #pragma unroll
             for (int j = 0; j < EXP_BATCH; ++j) cj[j] = __shfl_sync(0xffffffffu, c_reg, (e0 - loaded_base + j) & 31);
-            if (lane == 0) {
+            if (G4) {
+                if (lane == 0) {
+                    // whole boxes always: 4 rows x 128 floats per instruction (rows past the batch repeat its
+                    // first neighbour and are never read back; columns past ldx arrive as zeros)
+                    const int n4 = (cnt + 3) >> 2;
+                    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;"
+                                 :: "r"(bar), "r"((uint32_t)n4 * 4u * EXP_SW * 4u) : "memory");
+#pragma unroll
+                    for (int q = 0; q < EXP_BATCH / 4; ++q) {
+                        if (q < n4) {
+                            const int32_t r0 = cj[4 * q] & 0x7fffffff;
+                            const int32_t r1 = (4 * q + 1 < cnt) ? (cj[4 * q + 1] & 0x7fffffff) : r0;
+                            const int32_t r2 = (4 * q + 2 < cnt) ? (cj[4 * q + 2] & 0x7fffffff) : r0;
+                            const int32_t r3 = (4 * q + 3 < cnt) ? (cj[4 * q + 3] & 0x7fffffff) : r0;
+                            asm volatile("cp.async.bulk.tensor.2d.shared::cta.global.tile::gather4.mbarrier::complete_tx::bytes "
+                                         "[%0], [%1, {%2, %3, %4, %5, %6}], [%7];"
+                                         :: "r"(exp_smem_u32(&stage[wic][d][4 * q][0])), "l"(&tmap), "r"(f0), "r"(r0), "r"(r1),
+                                            "r"(r2), "r"(r3), "r"(bar)
+                                         : "memory");
+                        }
+                    }
+                }
+            } else if (lane == 0) {
                 asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;"
                              :: "r"(bar), "r"(bytes * (uint32_t)cnt) : "memory");
 #pragma unroll
@@ -163,10 +188,56 @@ spmm_hop_bulk_gather_kernel(const HopDev p, const int64_t n_tasks)
 
 using namespace sgc;
 
+// cuTensorMapEncodeTiled through the runtime's driver entry point (the library does not link libcuda)
+typedef CUresult (*encode_tiled_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                    const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static int32_t make_gather_map(CUtensorMap *map, const float *x, int64_t ldx, int64_t rows)
+{
+    static encode_tiled_fn encode = nullptr;
+    if (!encode) {
+        void *fn = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        SGC_CUDA_TRY(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q));
+        SGC_REQUIRE(fn && q == cudaDriverEntryPointSuccess, "exp_hop: cuTensorMapEncodeTiled is not available");
+        encode = reinterpret_cast<encode_tiled_fn>(fn);
+    }
+    const cuuint64_t dims[2] = {(cuuint64_t)ldx, (cuuint64_t)rows};
+    const cuuint64_t strides[1] = {(cuuint64_t)ldx * sizeof(float)};
+    const cuuint32_t box[2] = {(cuuint32_t)EXP_SW, 1u};
+    const cuuint32_t estr[2] = {1u, 1u};
+    const CUresult r = encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float *>(x), dims, strides, box, estr,
+                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("exp_hop: cuTensorMapEncodeTiled failed (%d)", (int)r);
+        return SGC_ERR_CUDA;
+    }
+    return SGC_OK;
+}
+
+static int32_t exp_hop(const sgc_plan_t *plan, const sgc_hop_args_t *a, int32_t depth, int32_t ctas_per_sm, bool g4,
+                       void *stream);
+
 extern "C" {
 
 int32_t sgc_exp_spmm_hop_bulk_gather(const sgc_plan_t *plan, const sgc_hop_args_t *a, int32_t depth,
                                      int32_t ctas_per_sm, void *stream)
+{
+    return exp_hop(plan, a, depth, ctas_per_sm, false, stream);
+}
+
+int32_t sgc_exp_spmm_hop_gather4(const sgc_plan_t *plan, const sgc_hop_args_t *a, int32_t depth,
+                                 int32_t ctas_per_sm, void *stream)
+{
+    return exp_hop(plan, a, depth, ctas_per_sm, true, stream);
+}
+
+}  // extern "C"
+
+static int32_t exp_hop(const sgc_plan_t *plan, const sgc_hop_args_t *a, int32_t depth, int32_t ctas_per_sm, bool g4,
+                       void *stream)
 {
     SGC_REQUIRE(plan && a, "exp_hop: null plan or args");
     const sgc_plan_impl *pl = &plan->impl;
@@ -200,20 +271,31 @@ int32_t sgc_exp_spmm_hop_bulk_gather(const sgc_plan_t *plan, const sgc_hop_args_
     if (depth < 1) depth = 1;
     if (depth > 3) depth = 3;
     const size_t smem = (size_t)(EXP_THREADS / 32) * depth * EXP_BATCH * EXP_SW * sizeof(float);
-#define SGC_EXP_LAUNCH(D)                                                                                        \
+    CUtensorMap tmap;
+    std::memset(&tmap, 0, sizeof(tmap));
+    if (g4) {
+        SGC_REQUIRE(a->ldx % 4 == 0, "exp_hop: gather4 needs a row pitch that is a multiple of 16 bytes");
+        int32_t rc = make_gather_map(&tmap, a->x_d, a->ldx, pl->n_cols);
+        if (rc != SGC_OK) return rc;
+    }
+#define SGC_EXP_LAUNCH(D, G)                                                                                     \
     do {                                                                                                         \
-        SGC_CUDA_TRY(cudaFuncSetAttribute(spmm_hop_bulk_gather_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+        SGC_CUDA_TRY(cudaFuncSetAttribute(spmm_hop_bulk_gather_kernel<D, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
                                           (int)smem));                                                           \
-        spmm_hop_bulk_gather_kernel<D><<<grid, EXP_THREADS, smem, s>>>(p, n_tasks);                            \
+        spmm_hop_bulk_gather_kernel<D, G><<<grid, EXP_THREADS, smem, s>>>(p, n_tasks, tmap);                     \
     } while (0)
-    if (depth == 1) SGC_EXP_LAUNCH(1);
-    else if (depth == 2) SGC_EXP_LAUNCH(2);
-    else SGC_EXP_LAUNCH(3);
+    if (g4) {
+        if (depth == 1) SGC_EXP_LAUNCH(1, true);
+        else if (depth == 2) SGC_EXP_LAUNCH(2, true);
+        else SGC_EXP_LAUNCH(3, true);
+    } else {
+        if (depth == 1) SGC_EXP_LAUNCH(1, false);
+        else if (depth == 2) SGC_EXP_LAUNCH(2, false);
+        else SGC_EXP_LAUNCH(3, false);
+    }
 #undef SGC_EXP_LAUNCH
     SGC_LAUNCH_CHECK();
     // Rows split into chunk items are left as partial sums (the product's fix-up kernel is not run): the
     // experiment times the gather kernel alone; tools/sweep_tma_gather.py checks results on a chunk = 0 plan.
     return SGC_OK;
 }
-
-}  // extern "C"

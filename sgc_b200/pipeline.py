@@ -29,6 +29,7 @@ values, split plans) runs while the features are still crossing PCIe.
     launched per block of output rows (row-slice views of the same CSR arrays, the same kernel) and
     block b is copied back while block b+1 is computed.
 """
+import contextlib
 import os
 import time
 
@@ -139,7 +140,7 @@ def _upload_shared(host, dtype, dev, group):
     return full[:nnz], (hi - lo) * host.element_size()
 
 
-def _uniform_value_shared(val_h, dev, group):
+def _uniform_value_shared(val_h, dev, group, stream=None):
     """`uniform_value` for an adjacency every rank of `group` holds in host memory: each rank compares
     its own 1/P of the values with the first one, and a one-word all-reduce (MIN) makes the verdict
     common -- every rank fills, or every rank uploads and all-gathers (a split decision would leave
@@ -157,9 +158,12 @@ def _uniform_value_shared(val_h, dev, group):
     lo, hi, _, world = _shared_piece(nnz, group)
     threads = max(1, host_threads() // world)
     same = hi <= lo or _ffi.lib().sgc_host_all_equal_f64(val_h.data_ptr() + 8 * lo, hi - lo, first, threads, 0) == 1
-    verdict = torch.tensor([1 if same else 0], dtype=torch.int32, device=dev)
-    dist.all_reduce(verdict, op=dist.ReduceOp.MIN, group=group)
-    return first if int(verdict.item()) == 1 else None
+    ctx = torch.cuda.stream(stream) if (stream is not None and dev.type == "cuda") else contextlib.nullcontext()
+    with ctx:
+        verdict = torch.tensor([1 if same else 0], dtype=torch.int32, device=dev)
+        dist.all_reduce(verdict, op=dist.ReduceOp.MIN, group=group)
+        agreed = int(verdict.item()) == 1
+    return first if agreed else None
 
 
 def host_threads():
@@ -217,8 +221,7 @@ def precompute_host(adj, features, degree, standardize=False, out=None, out_bloc
               adjacency is then uploaded once per node -- 1/P per rank -- and all-gathered over NVLink
     detect_uniform_values   scan the stored values on the host and, when they are all the same, fill the
               device array instead of uploading it (`uniform_value`; under `group` every rank scans its
-              own 1/P and a one-word all-reduce makes the verdict common); default: on, except under
-              `group`, where it measured neutral and is opt-in
+              own 1/P and a one-word all-reduce makes the verdict common); default: on
     stats     optional dict; receives h2d_bytes / d2h_bytes actually copied by this call,
               uniform_value (the fill value, or None when the values were uploaded) and scan_gave_up
               (True when the host scan ran out of its time budget in THIS call; no state is kept)
@@ -288,54 +291,57 @@ def precompute_host(adj, features, degree, standardize=False, out=None, out_bloc
             h2d = nbytes(rp_h) + nbytes(features)
             fill = None
             scan_report = {"scan_gave_up": False}
-            # under `group` the scan is opt-in: at N = 2 it measured neutral (16.3 vs 15.7 ms: the piece scan
-            # and the verdict's read-back stall the enqueueing thread for as long as the upload they save)
-            detect = (group is None) if detect_uniform_values is None else bool(detect_uniform_values)
+            detect = True if detect_uniform_values is None else bool(detect_uniform_values)
+            rp = rp_h.to(dev, non_blocking=True)
             if group is not None:
                 # all ranks hold the same adjacency in host memory (feature-sharded propagation): 1/P of
                 # `col` / `val` per rank over its own PCIe link + an NCCL all-gather over NVLink, instead of
                 # P times the bytes over PCIe (Reddit shape: 280 MB per GPU, 5 ms).  Collective.
-                rp = rp_h.to(dev, non_blocking=True)
                 col, up = _upload_shared(col_h, torch.int32, dev, group)
                 h2d += up
-                if detect:
-                    fill = _uniform_value_shared(val_h, dev, group)
-                    mark("values scanned", c_in)
-                if fill is not None:
-                    val = torch.full((val_h.numel(),), fill, dtype=torch.float64, device=dev)
-                else:
-                    val, up = _upload_shared(val_h, torch.float64, dev, group)
-                    h2d += up
             else:
-                rp = rp_h.to(dev, non_blocking=True)
                 col = col_h.to(dev, non_blocking=True)
                 h2d += nbytes(col_h)
-                if detect:
-                    ahead = nbytes(col_h)
-                    if by_cols:
-                        upload_slab(*slabs[0])                 # keeps the DMA engine fed during the host scan
-                        ahead += n * 4 * (slabs[0][1] - slabs[0][0])
+            # structure is up: when the values turn out to be constant the normalisation waits for this event
+            # only, and runs while the first feature slab is still crossing PCIe
+            csr_up = torch.cuda.Event()
+            csr_up.record(c_in)
+            if detect:
+                ahead = nbytes(col_h)
+                if by_cols:
+                    upload_slab(*slabs[0])                 # keeps the DMA engine fed during the host scan
+                    ahead += n * 4 * (slabs[0][1] - slabs[0][0])
+                if group is not None:
+                    # the verdict's all-reduce goes through the download stream (idle so far), so that it queues
+                    # behind the all-gather of `col` in NCCL's order but not behind the slab upload above
+                    fill = _uniform_value_shared(val_h, dev, group, c_out)
+                else:
                     fill = uniform_value(val_h, ahead, scan_report)
-                    mark("values scanned", c_in)
-                if fill is not None:
-                    val = torch.full((val_h.numel(),), fill, dtype=torch.float64, device=dev)
+                mark("values scanned", c_in)
+            val = None
+            if fill is None:
+                if group is not None:
+                    val, up = _upload_shared(val_h, torch.float64, dev, group)
+                    h2d += up
                 else:
                     val = val_h.to(dev, non_blocking=True)
                     h2d += nbytes(val_h)
-            csr_up = torch.cuda.Event()
-            csr_up.record(c_in)
+                csr_up = torch.cuda.Event()
+                csr_up.record(c_in)
             mark("csr up", c_in)
             for c0, c1 in slabs[len(x_up):]:
                 upload_slab(c0, c1)
             if stats is not None:
                 stats.update(h2d_bytes=int(h2d), d2h_bytes=int(n * f * 4), uniform_value=fill,
                              scan_gave_up=scan_report["scan_gave_up"])
-        for t in (rp, col, val):
+        for t in (rp, col) + (() if val is None else (val,)):
             t.record_stream(main)
         x.record_stream(c_in)
 
         # adjacency side, while the features are still on their way
         main.wait_event(csr_up)
+        if val is None:                                    # constant-valued adjacency: filled, not uploaded
+            val = torch.full((val_h.numel(),), fill, dtype=torch.float64, device=dev)
         graph = normalize_csr(n, rp, col, val)
         graph.values32()
         if by_cols:

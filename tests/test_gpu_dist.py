@@ -240,8 +240,12 @@ def host_worker(rank, world, port, ret):
                                         group=dist.group.WORLD, col_slab=64, stats=st2, detect_uniform_values=True)
         ok.append(st2["uniform_value"] is None and bool(torch.equal(got2, want2[:, c0:c1].cpu())))
         st3 = {}
-        got3 = sgc_b200.precompute_host(host, xh, k, standardize=True, group=dist.group.WORLD, col_slab=64, stats=st3)
-        ok.append(st3["uniform_value"] is None and bool(torch.equal(got3, got)))      # opt-in under `group`
+        got3 = sgc_b200.precompute_host(host, xh, k, standardize=True, group=dist.group.WORLD, col_slab=64, stats=st3,
+                                        detect_uniform_values=False)
+        ok.append(st3["uniform_value"] is None and bool(torch.equal(got3, got)))      # switched off per call
+        st4 = {}
+        got4 = sgc_b200.precompute_host(host, xh, k, standardize=True, group=dist.group.WORLD, col_slab=64, stats=st4)
+        ok.append(st4["uniform_value"] == float(host[3][0]) and bool(torch.equal(got4, got)))   # on by default
         ret[rank] = tuple(ok)
     finally:
         dist.destroy_process_group()
@@ -257,4 +261,4 @@ def test_host_pipeline_shared_adjacency_upload(world):
     ret = mp.Manager().dict()
     mp.spawn(host_worker, args=(world, free_port(), ret), nprocs=world, join=True)
     for rank in range(world):
-        assert ret[rank] == (True,) * 7, (rank, ret[rank])
+        assert ret[rank] == (True,) * 8, (rank, ret[rank])

@@ -1,6 +1,7 @@
 """EXPERIMENT (VERDICT r1 item 6c / SURVEY section 7 step 5): gathers of X staged through shared memory by the
 TMA unit (cp.async.bulk global -> shared per neighbour row piece, mbarrier completion, 1-3 batches of 8 pieces in
-flight per warp; sgc_exp_spmm_hop_bulk_gather) against the product hop kernel (per-lane LDG.128 gathers).
+flight per warp; sgc_exp_spmm_hop_bulk_gather -- and its tensor form, cp.async.bulk.tensor.2d tile::gather4, four rows
+per instruction through a CUtensorMap; sgc_exp_spmm_hop_gather4) against the product hop kernel (per-lane LDG.128 gathers).
 Checks bit-identity on a chunk = 0 plan first, then times both on the Reddit shape.
     python tools/sweep_tma_gather.py > profiles/r02_tma_gather_experiment.log"""
 import os, sys
@@ -13,17 +14,19 @@ from sgc_b200 import synth, _ffi
 from sgc_b200.propagate import _hop_args, _partial, default_hints
 from sgc_b200.graph import stream_ptr
 
+GATHER4 = os.environ.get("SGC_SWEEP_GATHER4", "1") != "0"
+GATHER4_OK = True
 dev = torch.device("cuda", 0)
 torch.cuda.set_device(dev)
 
 
-def exp_hop(graph, x, out, chunk, depth, ctas):
+def exp_hop(graph, x, out, chunk, depth, ctas, entry="sgc_exp_spmm_hop_bulk_gather"):
     plan = graph.plan(chunk)
     f = x.shape[1]
     partial = _partial(plan, f, dev)
     a = _hop_args(graph, plan, x.data_ptr(), x.stride(0), out.data_ptr(), out.stride(0), f, partial, None, None,
                   "inplace", 0, default_hints(), pad_owned=True)
-    _ffi.call("sgc_exp_spmm_hop_bulk_gather", plan.handle, _ffi.ctypes.byref(a), depth, ctas, stream_ptr())
+    _ffi.call(entry, plan.handle, _ffi.ctypes.byref(a), depth, ctas, stream_ptr())
     return partial
 
 
@@ -50,6 +53,16 @@ for f in (602, 128, 100):
         torch.cuda.synchronize()
         print("check f=%d depth=%d bit-identical to the product hop: %s" % (f, depth, bool(torch.equal(out, want))), flush=True)
         assert torch.equal(out, want)
+        if GATHER4:
+            out.fill_(-1.0)
+            exp_hop(g, x, out, 0, depth, 4, "sgc_exp_spmm_hop_gather4")
+            torch.cuda.synchronize()
+            same = bool(torch.equal(out, want))
+            print("check f=%d depth=%d tile::gather4 bit-identical to the product hop: %s" % (f, depth, same), flush=True)
+            if not same:
+                bad = (out != want).nonzero()
+                print("   first mismatches (row, col):", bad[:5].tolist(), "of", int(bad.shape[0]), flush=True)
+                GATHER4_OK = False
 del s, g
 # 2. timing at the Reddit shape
 s = synth.make_shape("reddit", device=dev)
@@ -64,3 +77,12 @@ for depth in (1, 2, 3):
             continue
         ms = t_ms(lambda: exp_hop(g, x, out, 512, depth, ctas))
         print("TMA-staged gathers depth=%d (%2d KB smem/CTA) %d CTAs/SM: %.3f ms" % (depth, depth * 16, ctas, ms), flush=True)
+if GATHER4 and GATHER4_OK:
+    for depth in (1, 2, 3):
+        for ctas in (3, 4, 5, 6, 7):
+            if depth * 16 * ctas > 220:
+                continue
+            ms = t_ms(lambda: exp_hop(g, x, out, 512, depth, ctas, "sgc_exp_spmm_hop_gather4"))
+            print("tile::gather4 (4 rows per TMA instruction) depth=%d (%2d KB smem/CTA) %d CTAs/SM: %.3f ms" % (depth, depth * 16, ctas, ms), flush=True)
+elif GATHER4:
+    print("tile::gather4 results differ from the product hop: not timed", flush=True)
