@@ -587,6 +587,7 @@ def choose_sharding(n, nnz, f, world, mem_bytes=170e9):
 # 602 columns would cost 0.62 ms, profiles/r01_sweep_block.log), splitting rows costs NVLink egress
 # (rows/P_r x (P_r - 1) row pushes per exchanging hop) that hides behind the gathers only while it is shorter
 # than them.  Reddit shape on 8 GPUs: 2 x 4.
+GRID_AUTO = False          # the cost model below picks the grid (else: the degenerate grid choose_sharding names)
 NVLINK_PUSH_BYTES_PER_MS = 5.5e8          # egress per GPU inside the fused hop (profiles/r02_nvlink_probe_n8_products.log)
 SLAB_PASS_MS_PER_ENTRY = 3.4e-8           # one 128-float slab pass over all stored entries (Reddit shape: 0.8 ms)
 
@@ -628,6 +629,8 @@ def choose_grid(n, nnz, f, k, world, mem_bytes=170e9):
         return 1, world
     if forced == "features":
         return world, 1
+    if not GRID_AUTO and os.environ.get("SGC_B200_GRID_AUTO", "0") != "1":
+        return (world, 1) if choose_sharding(n, nnz, f, world, mem_bytes) == "features" else (1, world)
     best = None
     for pc in range(1, world + 1):
         if world % pc:

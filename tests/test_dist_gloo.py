@@ -324,6 +324,7 @@ def test_choose_grid(monkeypatch):
     from sgc_b200 import dist as sd
     monkeypatch.delenv("SGC_B200_GRID", raising=False)
     monkeypatch.delenv("SGC_B200_SHARDING", raising=False)
+    monkeypatch.setenv("SGC_B200_GRID_AUTO", "1")
     for world in (1, 2, 4, 8):
         for shape in ((232965, 23.4e6, 602, 2), (2449029, 126e6, 100, 3), (111059956, 1.75e9, 128, 3), (19717, 1.1e5, 500, 2)):
             pc, pr = sd.choose_grid(*shape, world)

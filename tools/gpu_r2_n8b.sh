@@ -24,7 +24,7 @@ P
   grep -v "Warning\|warn\|\*\*\*\|OMP_NUM" gpurun_out/bench_n${N}_grid$grid.err | tail -4
 done
 port=$((port+1))
-timeout 600 $TR --master-port $port bench.py --gpus $N --steps 10 --warmup 3 ${FINAL_ARGS:-"--workload reddit"} > gpurun_out/bench_n$N.json 2> gpurun_out/bench_n$N.err
+SGC_B200_GRID_AUTO=1 timeout 600 $TR --master-port $port bench.py --gpus $N --steps 10 --warmup 3 ${FINAL_ARGS:-"--workload reddit"} > gpurun_out/bench_n$N.json 2> gpurun_out/bench_n$N.err
 echo "default line rc=$?" | tee -a gpurun_out/summary_n$N.txt
 head -c 2500 gpurun_out/bench_n$N.json; echo
 grep -v "Warning\|warn\|\*\*\*\|OMP_NUM" gpurun_out/bench_n$N.err | tail -6
