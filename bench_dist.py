@@ -398,6 +398,9 @@ def run_workload(name, args, rank, world, dev, B, lam=0.0, with_e2e=True, want_s
         return run_feature_sharded(name, args, rank, world, dev, B, lam, with_e2e)
     grid = sd.make_grid(shape["f"], p_cols, p_rows) if p_cols > 1 else None
     r = run_row_sharded(name, args, rank, world, dev, B, lam, with_e2e and not feature_e2e, want_single, steps, grid)
+    r["grid_model_ms"] = {"%dx%d" % (pc, world // pc): round(sd.grid_cost_ms(shape["n"], approx_nnz, shape["f"], shape["k"],
+                                                                              pc, world // pc), 3)
+                          for pc in range(1, world + 1) if world % pc == 0 and shape["f"] // pc >= 64}
     if with_e2e and feature_e2e:
         r["e2e"] = run_feature_sharded(name, args, rank, world, dev, B, lam, True, e2e_only=True)["e2e"]
         if r["e2e"] is not None:
@@ -514,7 +517,7 @@ def bench(args, rank, world, dev, B):
                        **{kk: (v.get("parity") or {}).get("ok") for kk, v in extras.items() if isinstance(v, dict) and "parity" in v},
                        "detail": r["parity"]},
             "details": {"parallelism": parallelism_text(r, world), "dist_mode": r["mode"],
-                        "grid_cols_x_rows": r.get("grid", [world, 1]),
+                        "grid_cols_x_rows": r.get("grid", [world, 1]), "grid_model_ms": r.get("grid_model_ms"),
                         "normalise_ms": r["normalise_ms"], "partition_locality_lambda": r["lam"],
                         "pushed_rows_x_peers_fraction": r["push_fraction"], "rows_per_rank": r["n_pad"],
                         "per_hop_breakdown": r["breakdown"]},
