@@ -237,6 +237,14 @@ int32_t sgc_spmm_plan_tag_hot(sgc_plan_t *plan, int64_t hot_rows, int32_t *col_t
                                      them with whole-vector stores (they receive zeros when the pad columns
                                      of x are zero).  Without the flag nothing beyond column f-1 is written,
                                      so y_d may be a column view of a wider live matrix.                */
+#define SGC_HOP_ACCUMULATE  16u   /* y_d += S_b x instead of y_d = S x: the plan describes ONE BLOCK OF COLUMNS
+                                     of S (a CSR holding only the entries whose column lies in the block) and
+                                     every row continues its running sum from the value y_d holds -- same
+                                     ascending-column FMA chain as the unblocked hop, so chunk = 0 results are
+                                     bit-identical; rows without entries in the block are not touched.  Launch
+                                     the blocks in ascending column order, the first one without the flag.
+                                     Keeps the gathered part of x (one block of its rows) L2-resident when x
+                                     is several times larger than L2.  Not with peer pushes / STD_*.       */
 
 typedef struct sgc_hop_args {
     const double *aval_d;      /* FUSED_NORM: fp64 values of A+I (pruned structure)          */

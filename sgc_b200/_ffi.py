@@ -17,6 +17,7 @@ HOP_FUSED_NORM = 1
 HOP_STD_DIV = 2
 HOP_STD_RCP = 4
 HOP_PAD_OWNED = 8
+HOP_ACCUMULATE = 16
 MAX_PEERS = 15
 IPC_HANDLE_BYTES = 64
 

@@ -69,7 +69,7 @@ __global__ void __launch_bounds__(256)
 spmm_fixup_kernel(int64_t n_long_rows, const int32_t *__restrict__ lr_row,
                   const int64_t *__restrict__ lr_first, const int32_t *__restrict__ lr_cnt,
                   const float *__restrict__ partial, int64_t ldp, float *__restrict__ y,
-                  int64_t ldy, int32_t f, PeerList peers)
+                  int64_t ldy, int32_t f, PeerList peers, int32_t accumulate)
 {
     const int64_t k = blockIdx.x;
     if (k >= n_long_rows) return;
@@ -77,6 +77,7 @@ spmm_fixup_kernel(int64_t n_long_rows, const int32_t *__restrict__ lr_row,
     const int cnt = lr_cnt[k];
     for (int c = threadIdx.x; c < f; c += blockDim.x) {
         float acc = partial[first * ldp + c];
+        if (accumulate) acc = __fadd_rn(y[row * ldy + c], acc);       // column-blocked hop: onto the earlier blocks' sum
         for (int j = 1; j < cnt; ++j) acc = __fadd_rn(acc, partial[(first + j) * ldp + c]);
         y[row * ldy + c] = acc;
         const uint32_t need = peers.mask ? peers.mask[row] : 0xffffffffu;
@@ -248,6 +249,9 @@ static int32_t run_hop(const sgc_plan_impl *pl, const sgc_hop_args_t *a, const f
     // whole-vector stores may spill into columns [f, round4(f)) only when the caller owns them as padding
     const bool pad_owned = (flags & SGC_HOP_PAD_OWNED) != 0 && (a->f + 3) / 4 * 4 <= ldy;
     p.f_store = pad_owned ? (a->f + 3) / 4 * 4 : a->f;
+    p.accumulate = (flags & SGC_HOP_ACCUMULATE) ? 1 : 0;
+    SGC_REQUIRE(!p.accumulate || (!peers_on && stdmode == 0),
+                "spmm_hop: SGC_HOP_ACCUMULATE excludes peer pushes and fused standardisation");
     p.hints = a->hints & (3 | 8 | 16 | 32 | 64);
     // keeping gathered rows with evict_last only helps when the slab can actually stay in L2
     if (!slab_fits_l2(pl->n_cols, slab < a->f ? slab : a->f)) p.hints &= ~1;
@@ -289,7 +293,8 @@ static int32_t run_hop(const sgc_plan_impl *pl, const sgc_hop_args_t *a, const f
     if (rc != SGC_OK) return rc;
     if (pl->n_long_rows > 0) {
         spmm_fixup_kernel<<<(unsigned)pl->n_long_rows, 256, 0, s>>>(
-            pl->n_long_rows, pl->lr_row, pl->lr_first, pl->lr_cnt, a->partial_d, a->ldp, y, ldy, a->f, peers);
+            pl->n_long_rows, pl->lr_row, pl->lr_first, pl->lr_cnt, a->partial_d, a->ldp, y, ldy, a->f, peers,
+            p.accumulate);
         SGC_LAUNCH_CHECK();
     }
     return SGC_OK;

@@ -57,6 +57,8 @@ struct HopDev {
     int32_t tpw;         // K5: tasks per tile and group slot of the peer variant (rows per tile = tpw * 32/G)
     int32_t stage_stride;// K5: floats between staged rows (ldy when tiles are contiguous in y, else the slab width)
     unsigned long long *tile_counter;   // [2]: next ticket, finished warps (zero between launches); null: one-shot grid
+    int32_t accumulate;  // column-blocked hop: rows ADD onto what y holds (acc starts from y, rows without entries
+                         // in this block are left alone); chunk items still start from 0, the fix-up adds them
     int32_t n_peers;     // K5: copies of y in other GPUs' memory that receive every output row
     float *peer_y[SGC_MAX_PEERS];
     const uint32_t *peer_mask;   // per-row bit set of peers that need the row (null: all)
@@ -242,6 +244,10 @@ __device__ __forceinline__ void hop_task(const HopDev &p, const int64_t task, co
         }
     }
     if (!valid) beg = end = 0;
+    // column-blocked hop (sgc_b200/propagate.py: hop_col_blocked): this launch covers one block of S's columns
+    // and continues the row's sum where the previous block's launch left it -- same FMA chain, same order
+    const bool accum = p.accumulate != 0 && to_y;
+    if (accum && valid && beg == end) valid = false;     // nothing in this block: y keeps its value
 
     const int f0 = (int)slab * SW;
     int fo_ld[U];
@@ -267,6 +273,21 @@ __device__ __forceinline__ void hop_task(const HopDev &p, const int64_t task, co
     for (int u = 0; u < U; ++u)
 #pragma unroll
         for (int v = 0; v < VEC; ++v) o.acc[u][v] = 0.f;
+    if (accum && valid) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            if (!o.act[u]) continue;
+            const float *q = dst + o.fo[u];
+            if (VEC == 4 && p.y_vec == 4 && o.fo[u] + 4 <= p.f_store) {
+                const float4 t = *reinterpret_cast<const float4 *>(q);
+                o.acc[u][0] = t.x; o.acc[u][1 % VEC] = t.y; o.acc[u][2 % VEC] = t.z; o.acc[u][3 % VEC] = t.w;
+            } else {
+#pragma unroll
+                for (int v = 0; v < VEC; ++v)
+                    if (o.fo[u] + v < p.f) o.acc[u][v] = q[v];
+            }
+        }
+    }
 
     const double di = (FUSED && valid) ? p.dinv_rows[row] : 0.0;
     const int len = (int)(end - beg);

@@ -115,6 +115,41 @@ class SgcGraph(object):
         self._plans[chunk] = (plan,)
         return plan
 
+    # -- column blocks (operands several times larger than L2) -----------------------------------
+    def col_blocks(self, n_blocks):
+        """[(c0, c1, SgcGraph)]: S split into `n_blocks` blocks of consecutive COLUMNS, each block a compacted
+        CSR of the entries whose column lies in [c0, c1) (global column ids kept; fp32 S values copied, so the
+        blocks together hold one more copy of col / sval plus n_blocks row-pointer arrays).  Entries of a row
+        keep their ascending order inside every block, which is what lets `propagate.hop_col_blocked` continue
+        each row's FMA chain block by block.  Cached per n_blocks.  Each block reports `n_cols` = the number of
+        rows of X it gathers from, so that the hop sizes its L2 policy for the block, not for all of X."""
+        n_blocks = max(1, min(int(n_blocks), max(self.n_cols, 1)))
+        hit = self._plans.get(("col_blocks", n_blocks))
+        if hit is not None:
+            return hit
+        dev = self.device
+        sval = self.values32()
+        per = (self.n_cols + n_blocks - 1) // n_blocks
+        per = (per + 127) // 128 * 128
+        with torch.cuda.device(dev):
+            rows = torch.empty(self.nnz, dtype=torch.int32, device=dev)
+            _ffi.call("sgc_csr_expand_rows", self.n_rows, _ffi.ptr(self.row_ptr), 0, _ffi.ptr(rows), stream_ptr())
+            blk = torch.div(self.col, per, rounding_mode="floor")
+            out = []
+            for b in range(n_blocks):
+                c0, c1 = b * per, min((b + 1) * per, self.n_cols)
+                if c1 <= c0:
+                    break
+                keep = (blk == b).nonzero().squeeze(1)
+                counts = torch.bincount(rows[keep].long(), minlength=self.n_rows)
+                rp = torch.zeros(self.n_rows + 1, dtype=torch.int64, device=dev)
+                torch.cumsum(counts, 0, out=rp[1:])
+                g = SgcGraph(self.n_rows, c1 - c0, rp, self.col[keep].contiguous(), None, None,
+                             sval=sval[keep].contiguous())
+                out.append((c0, c1, g))
+        self._plans[("col_blocks", n_blocks)] = out
+        return out
+
     # -- views -------------------------------------------------------------------------------
     def values32(self):
         """fp32 values of S: fp32((d_i*a_ij)*d_j), the single rounding of utils.py:25."""

@@ -141,6 +141,52 @@ def _check_out(g, out, f):
         raise ValueError("out must have unit column stride and a row stride of at least F")
 
 
+def col_blocks_for(g, row_bytes):
+    """How many column blocks a hop over an operand with `row_bytes`-long rows should take (SGC_B200_COL_BLOCKS):
+    0 / 1 = the plain single-pass hop (default); N >= 2 = that many; 'auto' = as many as make one block of the
+    gathered operand fit the L2 budget, for operands between 2x and 64x that budget whose rows are one slab
+    wide (products-like: N = 2.45 M rows of 416 bytes = 1 GB -> 10 blocks); wider operands take feature slabs,
+    larger ones would re-read y too often."""
+    from .graph import L2_SLAB_BUDGET
+    env = _ENV("SGC_B200_COL_BLOCKS", "0")
+    if env != "auto":
+        return max(0, int(env))
+    total = g.n_cols * int(row_bytes)
+    if row_bytes > 128 * 4 or total < 2 * L2_SLAB_BUDGET or total > 64 * L2_SLAB_BUDGET:
+        return 0
+    return int((total + 0.8 * L2_SLAB_BUDGET - 1) // (0.8 * L2_SLAB_BUDGET))
+
+
+def hop_col_blocked(g, x, n_blocks, chunk=None, hints=None, out=None, pad_owned=False):
+    """One hop ``S @ x`` as `n_blocks` launches, one per block of S's columns (SgcGraph.col_blocks), each adding
+    its block's contribution onto y (SGC_HOP_ACCUMULATE): the rows of x a launch gathers from are one
+    contiguous block small enough to stay in L2, where the single-pass hop on an operand several times larger
+    than L2 misses on most gathers (products shape: 45 GB of DRAM traffic per hop against 3 GB of compulsory
+    bytes).  The price is that y is read and re-written once per block.  Every row's sum is the same ascending-
+    column FMA chain as in the single-pass hop, continued from y: bit-identical with chunk = 0; with row
+    splitting the chunk boundaries fall inside the blocks, so split rows agree within north_star's tolerance."""
+    dev = require_cuda(g.device)
+    x = _check_features(g, x)
+    f = int(x.shape[1])
+    if out is not None:
+        _check_out(g, out, f)
+    chunk = default_chunk() if chunk is None else chunk
+    hints = default_hints() if hints is None else hints
+    with torch.cuda.device(dev):
+        y = out if out is not None else torch.empty((g.n_rows, f), dtype=torch.float32, device=dev)
+        if f == 0 or g.n_rows == 0:
+            return y
+        for i, (c0, c1, blk) in enumerate(g.col_blocks(n_blocks)):
+            plan = blk.plan(chunk)
+            partial = _partial(plan, f, dev)
+            a = _hop_args(blk, plan, x.data_ptr(), x.stride(0), y.data_ptr(), y.stride(0), f, partial, None, None,
+                          "inplace", 0, hints & ~4, pad_owned=pad_owned)
+            if i > 0:
+                a.flags |= _ffi.HOP_ACCUMULATE
+            _ffi.call("sgc_spmm_hop", plan.handle, _ffi.ctypes.byref(a), stream_ptr())
+    return y
+
+
 def hop(adj, x, mean=None, std=None, chunk=None, slab=None, hints=None, std_mode=None, out=None, peers=None,
         peer_mask=None, pad_owned=False):
     """One hop ``S @ x`` (torch.spmm(adj, x), utils.py:95).  Returns a new [n_rows, F] fp32
@@ -160,6 +206,10 @@ def hop(adj, x, mean=None, std=None, chunk=None, slab=None, hints=None, std_mode
         _check_out(g, out, f)
     if mean is not None:
         mean, std = mean.to(dev, torch.float32).contiguous(), std.to(dev, torch.float32).contiguous()
+    if mean is None and not peers and not slab:
+        nb = col_blocks_for(g, _pad8(f) * 4)
+        if nb >= 2:
+            return hop_col_blocked(g, x, nb, chunk=chunk, hints=hints, out=out, pad_owned=pad_owned)
     with torch.cuda.device(dev):
         y = out if out is not None else torch.empty((g.n_rows, f), dtype=torch.float32, device=dev)
         if f == 0 or g.n_rows == 0:
@@ -198,6 +248,29 @@ def propagate(adj, x, degree, mean=None, std=None, chunk=None, slab=None, hints=
                 return hop_sparse_x(g, sf, out=y)
             first = hop_sparse_x(g, sf)
         return propagate(g, first, degree - 1, chunk=chunk, slab=slab, hints=hints)
+    if mean is None and not slab and n > 0 and f > 0 and col_blocks_for(g, _pad8(f) * 4) >= 2:
+        # column-blocked hops (operand several times larger than L2): hop by hop through `hop`
+        with torch.cuda.device(dev):
+            ld = _pad8(f)
+            cur = x if (x.stride(0) % 4 == 0 and x.data_ptr() % 16 == 0) else None
+            if cur is None:
+                from .features import to_padded
+                cur = to_padded(x)
+            bufs = []
+            for k in range(degree):
+                last = k == degree - 1
+                if last:
+                    dst = torch.empty((n, f), dtype=torch.float32, device=dev)
+                else:
+                    if len(bufs) < 2:
+                        b = torch.empty((n, ld), dtype=torch.float32, device=dev)
+                        if ld != f:
+                            b[:, f:].zero_()
+                        bufs.append(b)
+                    dst = bufs[k & 1][:, :f]
+                hop(g, cur, chunk=chunk, hints=hints, out=dst, pad_owned=not last)
+                cur = dst
+            return cur
     with torch.cuda.device(dev):
         y = torch.empty((n, f), dtype=torch.float32, device=dev)
         if f == 0 or n == 0:

@@ -29,7 +29,11 @@ def preprocess_adj(adj):
     """``normalize_adj(adj + sp.eye(n))`` (utils.py:68-71) on the GPU: K1 inserts the self-loops,
     K2 the degrees, and the values are formed as (a_ij * d_j) * d_i -- the association of
     ``adj.dot(D).transpose().dot(D).transpose()`` (utils.py:66).  Returns an `SgcGraph`;
-    ``.tocoo()`` gives the reference's return value."""
+    ``.tocoo()`` gives the reference's return value.  The sibling packages (downstream/TextSGC_Bio,
+    TextSGC_indexing, TextSGC_ref: utils.py:108-112 there) share normalize_adj / sgc_precompute line for
+    line and only append ``.astype(np.float32)`` here -- the rounding `sparse_to_torch_sparse` applies
+    anyway (utils.py:112), and the one the graph's fp32 S values already carry -- so this mirror serves them
+    unchanged."""
     if isinstance(adj, SgcGraph):
         return adj
     return from_scipy(adj, order=1)

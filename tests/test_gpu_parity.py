@@ -242,6 +242,47 @@ def test_hot_column_tags(dev, monkeypatch):
     assert plan.col_tagged is None and torch.equal(again, base)
 
 
+@pytest.mark.parametrize("f", [100, 130, 7])
+def test_column_blocked_hop(dev, monkeypatch, f):
+    """Column-blocked hop (SGC_HOP_ACCUMULATE; operands several times larger than L2): every block's launch
+    continues the rows' FMA chains from y, so exact mode (chunk=0) is bit-identical to the single-pass hop and
+    to the oracle for any number of blocks; with row splitting, split rows stay within tolerance and results are
+    deterministic; blocks tile the stored entries; the K-hop driver takes the same path hop by hop."""
+    import sgc_b200
+    from sgc_b200.propagate import hop_col_blocked
+    from oracle import spmm_oracle as so
+    s, graph = powerlaw_case(dev, scale=0.02, seed=17)
+    n = graph.n_rows
+    x = s["x"][:, :f].contiguous()
+    rp, col, val = graph.row_ptr.cpu().numpy(), graph.col.cpu().numpy(), graph.values32().cpu().numpy()
+    monkeypatch.setenv("SGC_B200_COL_BLOCKS", "0")
+    plain = sgc_b200.hop(graph, x, chunk=0)
+    assert np.array_equal(plain.cpu().numpy(), so.spmm_hop(rp, col, val, x.cpu().numpy()))
+    for nb in (2, 3, 7, 33):
+        blocks = graph.col_blocks(nb)
+        assert sum(b.nnz for _, _, b in blocks) == graph.nnz
+        assert all(int(b.col.min()) >= c0 and int(b.col.max()) < c1 for c0, c1, b in blocks if b.nnz)
+        assert all(a[1] == b[0] for a, b in zip(blocks, blocks[1:])) and blocks[0][0] == 0 and blocks[-1][1] == n
+        got = hop_col_blocked(graph, x, nb, chunk=0)
+        assert torch.equal(got, plain), nb
+        # into a column view of a wider live matrix: neighbours untouched
+        wide = torch.full((n, f + 9), -3.0, device=dev)
+        hop_col_blocked(graph, x, nb, chunk=0, out=wide[:, 4:4 + f])
+        assert torch.equal(wide[:, 4:4 + f], plain) and bool((wide[:, :4] == -3.0).all()) and bool((wide[:, 4 + f:] == -3.0).all())
+        split_a = hop_col_blocked(graph, x, nb, chunk=64)
+        split_b = hop_col_blocked(graph, x, nb, chunk=64)
+        assert torch.equal(split_a, split_b)
+        assert np.allclose(split_a.cpu().numpy(), plain.cpu().numpy(), rtol=RTOL, atol=ATOL)
+    # the K-hop entry points, switched by the environment
+    want, _ = sgc_b200.sgc_precompute(x, graph, 3, chunk=0)
+    monkeypatch.setenv("SGC_B200_COL_BLOCKS", "5")
+    got, _ = sgc_b200.sgc_precompute(x, graph, 3, chunk=0)
+    assert torch.equal(got, want)
+    assert torch.equal(sgc_b200.hop(graph, x, chunk=0), plain)
+    monkeypatch.setenv("SGC_B200_COL_BLOCKS", "auto")          # small operand: auto keeps the single pass
+    assert sgc_b200.propagate.col_blocks_for(graph, 416) == 0
+
+
 def test_fused_norm_mode_is_bit_identical(dev, monkeypatch):
     """SGC_B200_FUSED_NORM=1 (weights formed in the kernel from fp64 A+I values and D^-1/2; S is
     never materialised) and the default (fp32 S values written once by sgc_norm_values at
