@@ -21,3 +21,5 @@ head -c 1500 gpurun_out/bench_ref.json; echo
 cat gpurun_out/summary.txt
 timeout 400 python tools/sweep_tma_gather.py > gpurun_out/tma_gather.log 2>&1; echo "tma rc=$?" | tee -a gpurun_out/summary.txt
 grep -v "Warn\|warn" gpurun_out/tma_gather.log | tail -45
+timeout 500 python tools/sweep_col_blocks.py products > gpurun_out/col_blocks.log 2>&1; echo "col blocks rc=$?" | tee -a gpurun_out/summary.txt
+grep -v "Warn\|warn" gpurun_out/col_blocks.log | tail -16
