@@ -50,25 +50,6 @@ def _copy_streams_for(dev):
     return s
 
 
-_extra_streams = {}
-
-
-def copy_lanes():
-    """Copy streams per direction for the strided slab copies (SGC_B200_COPY_LANES, default 1).  A slab copy is
-    a 2-D DMA transfer of 512-byte pieces at the host matrix's row pitch; split by rows over several streams
-    the pieces are issued by several copy engines at once (tools/copy2d_probe2.py measures what that buys)."""
-    return max(1, min(4, int(os.environ.get("SGC_B200_COPY_LANES", "1"))))
-
-
-def _lanes_for(dev, first, which, n):
-    """`n` streams of direction `which` (0 in, 1 out); lane 0 is the pipeline's own copy stream."""
-    key = (dev.index, which)
-    extra = _extra_streams.setdefault(key, [])
-    while len(extra) < n - 1:
-        extra.append(torch.cuda.Stream(device=dev))
-    return [first] + extra[:n - 1]
-
-
 def default_out_blocks():
     """Row blocks of the last hop (SGC_B200_OUT_BLOCKS; 1 = one launch, then one D2H)."""
     return max(1, int(os.environ.get("SGC_B200_OUT_BLOCKS", "8")))
@@ -286,11 +267,8 @@ def precompute_host(adj, features, degree, standardize=False, out=None, out_bloc
 
         x = padded_rows(n, f, dev)
         ld = x.stride(0)
-        n_lanes = copy_lanes()
-        in_lanes, out_lanes = _lanes_for(dev, c_in, 0, n_lanes), _lanes_for(dev, c_out, 1, n_lanes)
-        lane_rows = [min(n, ((n + n_lanes - 1) // n_lanes) * i) for i in range(n_lanes + 1)]
-        for lane in in_lanes + out_lanes:
-            lane.wait_stream(main)
+        c_in.wait_stream(main)
+        c_out.wait_stream(main)
         mark("start", main)
         starts = [sum(widths[:i]) for i in range(len(widths))]
         slabs = [(c0, c0 + w) for c0, w in zip(starts, widths)]
@@ -299,28 +277,14 @@ def precompute_host(adj, features, degree, standardize=False, out=None, out_bloc
             x_up = []
 
             def upload_slab(c0, c1):
-                evs = []
                 if by_cols:
-                    # rows dealt to the copy lanes; lanes > 0 start where lane 0 stands now (after the CSR)
-                    here = torch.cuda.Event()
-                    here.record(c_in)
-                    for i, lane in enumerate(in_lanes):
-                        r0, r1 = lane_rows[i], lane_rows[i + 1]
-                        if r1 <= r0:
-                            continue
-                        if i:
-                            lane.wait_event(here)
-                        _ffi.call("sgc_copy_2d", x.data_ptr() + 4 * (r0 * ld + c0), 4 * ld,
-                                  features.data_ptr() + 4 * (r0 * f + c0), 4 * f, 4 * (c1 - c0), r1 - r0, lane.cuda_stream)
-                        e = torch.cuda.Event()
-                        e.record(lane)
-                        evs.append(e)
+                    _ffi.call("sgc_copy_2d", x.data_ptr() + 4 * c0, 4 * ld, features.data_ptr() + 4 * c0, 4 * f,
+                              4 * (c1 - c0), n, c_in.cuda_stream)
                 else:
                     x.copy_(features, non_blocking=True)       # whole rows: one contiguous transfer
-                    e = torch.cuda.Event()
-                    e.record(c_in)
-                    evs.append(e)
-                x_up.append(evs)
+                e = torch.cuda.Event()
+                e.record(c_in)
+                x_up.append(e)
                 mark("x[:, %d:%d] up" % (c0, c1), c_in)
 
             nbytes = lambda t: t.numel() * t.element_size()
@@ -372,8 +336,7 @@ def precompute_host(adj, features, degree, standardize=False, out=None, out_bloc
                              scan_gave_up=scan_report["scan_gave_up"])
         for t in (rp, col) + (() if val is None else (val,)):
             t.record_stream(main)
-        for lane in in_lanes:
-            x.record_stream(lane)
+        x.record_stream(c_in)
 
         # adjacency side, while the features are still on their way
         main.wait_event(csr_up)
@@ -399,8 +362,7 @@ def precompute_host(adj, features, degree, standardize=False, out=None, out_bloc
         # column slabs land in padded rows (aligned vector stores; the strided D2H drops the padding);
         # whole-row blocks go back as contiguous pieces
         y = padded_rows(n, f, dev) if by_cols else torch.empty((n, f), dtype=torch.float32, device=dev)
-        for lane in out_lanes:
-            y.record_stream(lane)
+        y.record_stream(c_out)
 
         def back(r0, r1, c0, c1):
             done = torch.cuda.Event()
@@ -408,22 +370,15 @@ def precompute_host(adj, features, degree, standardize=False, out=None, out_bloc
             c_out.wait_event(done)
             mark("y[%d:%d, %d:%d] computed" % (r0, r1, c0, c1), main)
             if by_cols:
-                for i, lane in enumerate(out_lanes):
-                    a, b = max(r0, lane_rows[i]), min(r1, lane_rows[i + 1])
-                    if b <= a:
-                        continue
-                    if i:
-                        lane.wait_event(done)
-                    _ffi.call("sgc_copy_2d", out.data_ptr() + 4 * (a * f + c0), 4 * f,
-                              y.data_ptr() + 4 * (a * ld + c0), 4 * ld, 4 * (c1 - c0), b - a, lane.cuda_stream)
+                _ffi.call("sgc_copy_2d", out.data_ptr() + 4 * (r0 * f + c0), 4 * f,
+                          y.data_ptr() + 4 * (r0 * ld + c0), 4 * ld, 4 * (c1 - c0), r1 - r0, c_out.cuda_stream)
             else:
                 with torch.cuda.stream(c_out):
                     out[r0:r1].copy_(y[r0:r1], non_blocking=True)
             mark("y[%d:%d, %d:%d] down" % (r0, r1, c0, c1), c_out)
 
-        for (c0, c1), ups in zip(slabs, x_up):
-            for up in ups:
-                main.wait_event(up)
+        for (c0, c1), up in zip(slabs, x_up):
+            main.wait_event(up)
             cur = x[:, c0:c1]
             if standardize:
                 mean, std = col_stats(cur)
@@ -440,10 +395,8 @@ def precompute_host(adj, features, degree, standardize=False, out=None, out_bloc
                 for r0, r1, sub in blocks:
                     hop(sub, cur, chunk=chunk, out=y[r0:r1, c0:c1])
                     back(r0, r1, c0, c1)
-        for lane in out_lanes:
-            main.wait_stream(lane)
-        for lane in out_lanes:
-            lane.synchronize()
+        main.wait_stream(c_out)
+        c_out.synchronize()
         if trace is not None:
             main.synchronize()
             # (label, device ms since the start mark, host ms since the call when the mark was enqueued)

@@ -66,12 +66,6 @@ for slab in (64, 128, 256):
 for ws in ([128] * 4 + [90], [128] * 4 + [64, 26], [64] + [128] * 4 + [26]):
     ms = timeit(lambda: sgc_b200.precompute_host(csr, host["x"], k, standardize=True, out=out, col_slab=ws))
     print("column-slab schedule, widths=%s: %.2f ms   identical: %s" % (ws, ms, torch.equal(out, ref)))
-for lanes in ("1", "2", "3", "4"):
-    os.environ["SGC_B200_COPY_LANES"] = lanes
-    ms = timeit(lambda: sgc_b200.precompute_host(csr, host["x"], k, standardize=True, out=out))
-    print("column-slab schedule, default widths, %s copy lane(s) per direction: %.2f ms   identical: %s"
-          % (lanes, ms, torch.equal(out, ref)))
-os.environ.pop("SGC_B200_COPY_LANES", None)
 tr = []
 sgc_b200.precompute_host(csr, host["x"], k, standardize=True, out=out, trace=tr)
 print("device-side timeline of the default schedule (ms since start):")
