@@ -245,6 +245,7 @@ static int32_t run_hop(const sgc_plan_impl *pl, const sgc_hop_args_t *a, const f
     p.n_rows = pl->n_rows; p.n_long_items = pl->n_long_items;
     p.f = a->f; p.chunk = pl->chunk;
     p.n_slabs = (a->f + slab - 1) / slab;
+    p.work = pl->nnz * (int64_t)p.n_slabs;
     p.y_vec = y_vec;
     // whole-vector stores may spill into columns [f, round4(f)) only when the caller owns them as padding
     const bool pad_owned = (flags & SGC_HOP_PAD_OWNED) != 0 && (a->f + 3) / 4 * 4 <= ldy;
@@ -252,7 +253,7 @@ static int32_t run_hop(const sgc_plan_impl *pl, const sgc_hop_args_t *a, const f
     p.accumulate = (flags & SGC_HOP_ACCUMULATE) ? 1 : 0;
     SGC_REQUIRE(!p.accumulate || (!peers_on && stdmode == 0),
                 "spmm_hop: SGC_HOP_ACCUMULATE excludes peer pushes and fused standardisation");
-    p.hints = a->hints & (3 | 8 | 16 | 32 | 64);
+    p.hints = a->hints & (3 | 8 | 16 | 32 | 64 | 256);
     // keeping gathered rows with evict_last only helps when the slab can actually stay in L2
     if (!slab_fits_l2(pl->n_cols, slab < a->f ? slab : a->f)) p.hints &= ~1;
     SGC_REQUIRE(a->n_peers >= 0 && a->n_peers <= SGC_MAX_PEERS, "spmm_hop: n_peers out of range");
@@ -278,13 +279,19 @@ static int32_t run_hop(const sgc_plan_impl *pl, const sgc_hop_args_t *a, const f
         SGC_REQUIRE(y_vec != 4 || a->f % 4 == 0 || pad_owned,
                     "spmm_hop: peer pushes of a width that is not a multiple of 4 floats need SGC_HOP_PAD_OWNED "
                     "(the bulk stores cover the pad columns)");
-        // rows per tile: push_tile_tasks tasks per group slot (default 8), at most 32 rows per warp tile
-        const int gpw = 32 / g;
-        int tpw = a->push_tile_tasks > 0 ? a->push_tile_tasks : 8;
-        if (tpw * gpw > 32) tpw = 32 / gpw;
-        p.tpw = tpw;
         // tiles are contiguous in y when one slab covers the whole padded row
         p.stage_stride = (p.n_slabs == 1 && ldy <= slab && y_vec == 4) ? (int32_t)ldy : slab;
+        // rows per tile: push_tile_tasks tasks per group slot, at most 32 rows per warp tile.  Default: 8 where a
+        // tile can leave as ONE bulk store (rows contiguous in the operand: bigger NVLink transactions, 1.53 vs
+        // 1.66 ms per fused products hop on 8 GPUs); 1 where every row piece is its own store anyway (feature
+        // slabs narrower than the row: Reddit shape) -- there a tile is only a scheduling quantum, and 8 tasks per
+        // ticket left a row part of 121 k tasks with 4 tickets per warp (1.62 ms per hop against 0.77 ms for the
+        // plain kernel, profiles/r02_grid_n8.log)
+        const int gpw = 32 / g;
+        const bool tiles = p.stage_stride == (int32_t)ldy;
+        int tpw = a->push_tile_tasks > 0 ? a->push_tile_tasks : (tiles ? 8 : 1);
+        if (tpw * gpw > 32) tpw = 32 / gpw;
+        p.tpw = tpw;
         SGC_REQUIRE(pl->tile_counter != nullptr, "spmm_hop: the plan has no workspace (needed by the peer variant)");
         p.tile_counter = pl->tile_counter;
     }

@@ -26,6 +26,7 @@
 namespace sgc {
 
 constexpr int HOP_THREADS = 128;
+constexpr int64_t TICKET_MIN_WORK = 2 * 1000 * 1000;      // gathers per launch above which the ticket grid pays
 
 struct HopDev {
     const int64_t *row_ptr;
@@ -57,6 +58,7 @@ struct HopDev {
     int32_t tpw;         // K5: tasks per tile and group slot of the peer variant (rows per tile = tpw * 32/G)
     int32_t stage_stride;// K5: floats between staged rows (ldy when tiles are contiguous in y, else the slab width)
     unsigned long long *tile_counter;   // [2]: next ticket, finished warps (zero between launches); null: one-shot grid
+    int64_t work;        // stored entries x feature slabs of this launch (grid policy: ticket grid vs one-shot)
     int32_t accumulate;  // column-blocked hop: rows ADD onto what y holds (acc starts from y, rows without entries
                          // in this block are left alone); chunk items still start from 0, the fix-up adds them
     int32_t n_peers;     // K5: copies of y in other GPUs' memory that receive every output row
@@ -618,9 +620,12 @@ int32_t launch_hop(const HopDev &p, int64_t n_tasks, cudaStream_t s)
             static int occ = 0;                         // per instantiation; the device type is fixed (sm_100a)
             if (occ == 0) SGC_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, HOP_THREADS, 0));
             const int64_t cap = (int64_t)sm_count() * (occ > 0 ? occ : 1);
-            // small problems (Cora, Pubmed: a few tasks per resident warp) are launch-bound and have no tail to
-            // speak of: one warp per task in a one-shot grid (Pubmed K=2: 0.092 ms vs 0.129 ms with tickets)
-            if (n_tasks > 32 * cap * (HOP_THREADS / 32) * GPW) {
+            // small problems (Cora, Pubmed: a few tasks per resident warp, a few 100 k gathers) are launch-bound and
+            // have no tail to speak of: one warp per task in a one-shot grid (Pubmed K=2: 0.092 ms vs 0.129 ms with
+            // tickets).  Otherwise tickets: by task count, or by work -- a row part of a sharded graph has few tasks
+            // per resident warp but millions of gathers (Reddit shape, a quarter of the rows x 2 slabs: 121 k tasks,
+            // 11.7 M gathers).  hints bit 8 forces tickets, bit 7 the one-shot grid (A/B measurements).
+            if (n_tasks > 32 * cap * (HOP_THREADS / 32) * GPW || p.work > TICKET_MIN_WORK || (p.hints & 256)) {
                 const int RT = p.tpw * GPW;
                 const int64_t n_tiles = ceil_div(n_tasks, RT);
                 const int64_t want = ceil_div(n_tiles, HOP_THREADS / 32);
