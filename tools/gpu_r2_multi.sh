@@ -7,11 +7,6 @@ mkdir -p gpurun_out
 nvidia-smi -L > gpurun_out/gpus_multi.txt
 : > gpurun_out/summary_multi.txt
 port=29560
-# two single-GPU probes ride along (GPU 0): strided slab copies vs streams / widths, column-blocked hop sweep
-timeout 200 python tools/copy2d_probe2.py > gpurun_out/copy2d_probe2.log 2>&1; echo "copy2d probe rc=$?" | tee -a gpurun_out/summary_multi.txt
-grep -v "Warn\|warn" gpurun_out/copy2d_probe2.log | tail -16
-timeout 400 python tools/sweep_col_blocks.py products > gpurun_out/col_blocks.log 2>&1; echo "col blocks rc=$?" | tee -a gpurun_out/summary_multi.txt
-grep -v "Warn\|warn" gpurun_out/col_blocks.log | tail -14
 run() {   # N grid push_rows
   local N=$1 grid=$2 rows=$3
   port=$((port+1))
@@ -30,8 +25,9 @@ except Exception as e:
 P
   grep -v "Warning\|warn\|\*\*\*\|OMP_NUM" gpurun_out/bench_$tag.err | tail -3
 }
-for cfg in ${CONFIGS:-"8:2x4:0 8:2x4:1 8:1x8:0 4:1x4:0 4:1x4:1 2:1x2:0 2:1x2:1"}; do
-  IFS=: read N grid rows <<< "$cfg"
+CONFIGS=${CONFIGS:-"8:2x4:0 8:1x8:0 8:4x2:0 4:1x4:0 4:2x2:0 2:1x2:0"}
+for cfg in $CONFIGS; do
+  N=${cfg%%:*}; rest=${cfg#*:}; grid=${rest%%:*}; rows=${rest#*:}
   run $N $grid $rows
 done
 port=$((port+1))
