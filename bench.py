@@ -765,6 +765,30 @@ def run_e2e(args, s, name, k, nnz_s, dev):
     with env_override(SGC_B200_UNIFORM_VALUES="0"):
         secs_w = measure()
     st_w = dict(stats)
+    # same call, X and the result in pinned staging buffers whose row pitch is a multiple of 64 bytes
+    # (sgc_b200.pipeline.pinned_rows: 2432 instead of 2408 bytes): the strided slab copies then start and end on
+    # cache-line boundaries
+    aligned = None
+    if len(widths) > 1:
+        xa, oa = sgc_b200.pipeline.pinned_rows(n, f), sgc_b200.pipeline.pinned_rows(n, f)
+        xa.copy_(host["x"])
+        plain_x, plain_out = host["x"], out_host
+
+        def step_aligned():
+            sgc_b200.precompute_host((n, host["row_ptr"], host["col"], host["val"]), xa, k,
+                                     standardize=bool(synth.SHAPES[name]["scaled"]), out=oa, stats=stats)
+
+        step_aligned()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            step_aligned()
+        secs_a = (time.perf_counter() - t0) / steps
+        aligned = {"value": k * nnz_s * f / secs_a, "ms_per_step": secs_a * 1e3,
+                   "same_bits_as_contiguous_layout": bool(torch.equal(oa, plain_out)),
+                   "what": "same call with X and the result in sgc_b200.pipeline.pinned_rows staging buffers (host row "
+                           "pitch %d bytes instead of %d: slab pieces start and end on 64-byte lines)"
+                           % (4 * xa.stride(0), 4 * f)}
+        del xa, oa
     host_bytes = sum(t.numel() * t.element_size() for t in host.values())
     values = ("the %d stored values of A are all %g (adj + adj.T of a 0/1 matrix, utils.py:116; found by a threaded "
               "exact scan on the host, inside the timed region, every step): filled on the GPU instead of uploaded "
@@ -779,6 +803,7 @@ def run_e2e(args, s, name, k, nnz_s, dev):
                                    "h2d_bytes_per_step": int(st_w["h2d_bytes"]),
                                    "what": "same call with SGC_B200_UNIFORM_VALUES=0: the value array of A is "
                                            "uploaded like any weighted adjacency's"},
+            "aligned_host_rows": aligned,
             "scan_gave_up": bool(st.get("scan_gave_up", False)),
             "path": "sgc_b200.precompute_host: pinned host CSR(A)+X -> H2D (row_ptr + col first; X in %s; %s) -> "
                     "aug_normalized_adjacency (K1,K2, overlapped with the upload of X) -> per slab: col_stats + "

@@ -588,27 +588,35 @@ def choose_sharding(n, nnz, f, world, mem_bytes=170e9):
 # (rows/P_r x (P_r - 1) row pushes per exchanging hop) that hides behind the gathers only while it is shorter
 # than them.  Reddit shape on 8 GPUs: 2 x 4.
 GRID_AUTO = False          # the cost model below picks the grid (else: the degenerate grid choose_sharding names)
+# Constants fitted to tools/sweep_rowpart.py on one B200 (profiles/r02_sweep_rowpart.log: the hop on a column block
+# and a row part of the Reddit shape, plain and peer variants) and to the 8-GPU exchange probes:
+SLAB_PASS_MS_PER_ENTRY = 3.5e-8           # one 128-float slab pass over all stored entries (Reddit shape: 0.82 ms)
+HOP_FIXED_MS = 0.07                       # launches (main + narrow remainder + fix-ups) and ramp of one hop
+PEER_VARIANT_FACTOR = 1.15                # peer variant vs plain kernel, pushes skipped
+PUSH_MS_PER_BYTE = 0.33e-9                # issuing the pushes + the HBM writes they cause at the receivers
 NVLINK_PUSH_BYTES_PER_MS = 5.5e8          # egress per GPU inside the fused hop (profiles/r02_nvlink_probe_n8_products.log)
-SLAB_PASS_MS_PER_ENTRY = 3.4e-8           # one 128-float slab pass over all stored entries (Reddit shape: 0.8 ms)
+ROWS_MUST_WIN_BY = 0.08                   # an exchanging grid is taken only when the model prefers it by this margin
 
 
 def _block_cost_slabs(w):
-    """Cost of one hop over a w-column block in units of a full 128-float slab pass (profiles/r01_sweep_block.log:
-    32 columns 0.47, 48-64 0.65, 80-96 0.92, 112-128 1.0; a remainder of at most 64 columns runs as its own
-    launch with narrower lane groups)."""
+    """Cost of one hop over a w-column block in units of a full 128-float slab pass: full slabs, plus the
+    remainder -- at most 64 columns run as their own launch with narrower lane groups at ~0.7 of a full pass
+    (304 columns = 2.7, 160 = 1.67, 80 = 0.92 passes measured), wider ones as one more (partly idle) slab."""
     full, r = divmod(int(w), 128)
-    rem = 0.0 if r == 0 else (0.47 if r <= 32 else (0.65 if r <= 64 else (0.92 if r <= 96 else 1.0)))
+    rem = 0.0 if r == 0 else (0.7 if r <= 64 else (0.92 if r <= 96 else 1.0))
     return full + rem
 
 
 def grid_cost_ms(n, nnz, f, k, p_cols, p_rows):
-    """Modelled time of K hops on a p_cols x p_rows grid (relative ranking of the grids; not a prediction)."""
+    """Modelled time of K hops on a p_cols x p_rows grid (ranks the grids; not a prediction)."""
     w = max(c1 - c0 for c0, c1 in partition_features(f, p_cols))
-    compute = SLAB_PASS_MS_PER_ENTRY * nnz * _block_cost_slabs(w) / p_rows
+    compute = SLAB_PASS_MS_PER_ENTRY * nnz * _block_cost_slabs(w) / p_rows + HOP_FIXED_MS
+    if p_rows == 1:
+        return k * compute
     rows = (n + p_rows - 1) // p_rows
-    exchange = rows * _pad8(w) * 4.0 * (p_rows - 1) / NVLINK_PUSH_BYTES_PER_MS
-    barrier = 0.04 if p_rows > 1 else 0.0
-    fused = 1.15 * max(compute, exchange) if p_rows > 1 else compute
+    pushed = rows * _pad8(w) * 4.0 * (p_rows - 1)
+    fused = max(PEER_VARIANT_FACTOR * compute + PUSH_MS_PER_BYTE * pushed, 1.1 * pushed / NVLINK_PUSH_BYTES_PER_MS)
+    barrier = 0.04
     return (k - 1) * (fused + barrier) + compute + barrier
 
 
@@ -642,6 +650,8 @@ def choose_grid(n, nnz, f, k, world, mem_bytes=170e9):
         if nnz / pr * 20.0 + n * 8.0 + 3.0 * n * _pad8(w) * 4.0 >= mem_bytes:
             continue
         cost = grid_cost_ms(n, nnz, f, k, pc, pr)
+        if pr > 1:
+            cost *= 1.0 + ROWS_MUST_WIN_BY      # feature sharding needs no exchange, no peer mappings, no barrier
         if best is None or cost < best[0] - 1e-9:
             best = (cost, pc, pr)
     if best is None:

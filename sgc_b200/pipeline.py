@@ -50,6 +50,17 @@ def _copy_streams_for(dev):
     return s
 
 
+def pinned_rows(n, f, align_bytes=64):
+    """Pinned fp32 [n, f] host matrix whose row pitch is a multiple of `align_bytes` (a column view of a wider
+    pinned buffer): a staging layout for `precompute_host`'s `features` / `out`.  A column slab of a row-major
+    matrix is a strided transfer of 512-byte pieces; with a 2408-byte pitch (602 floats) every piece starts and
+    ends inside a 64-byte line, with 2432 bytes none does: H2D 47.9 -> 54.2 GB/s, D2H 46.1 -> 52.3 GB/s, both
+    at once 34.6 -> 40.8 GB/s each way (profiles/r02_copy2d_probe2.log)."""
+    per = max(1, align_bytes // 4)
+    ld = (int(f) + per - 1) // per * per
+    return torch.empty((int(n), ld), dtype=torch.float32).pin_memory()[:, :int(f)]
+
+
 def default_out_blocks():
     """Row blocks of the last hop (SGC_B200_OUT_BLOCKS; 1 = one launch, then one D2H)."""
     return max(1, int(os.environ.get("SGC_B200_OUT_BLOCKS", "8")))
@@ -211,7 +222,9 @@ def precompute_host(adj, features, degree, standardize=False, out=None, out_bloc
 
     adj       scipy sparse matrix, or a tuple (n, row_ptr, col, val) of host tensors holding the
               CSR of A (int64 / int32 / float64; pinned memory makes the copies asynchronous)
-    features  host fp32 tensor [N, F], contiguous (pinned for asynchronous copies)
+    features  host fp32 tensor [N, F] with unit column stride (pinned for asynchronous copies).  Rows may be
+              padded: the strided slab copies run 13-18 % faster when the host row pitch is a multiple of 64 bytes
+              (`pinned_rows`; profiles/r02_copy2d_probe2.log) -- the same holds for `out`
     degree    K >= 1
     standardize   apply utils.py:119 ((x - mean) / std per column, unbiased std) before the hops
     out       optional pinned fp32 [N, F] host tensor receiving the result
@@ -238,12 +251,16 @@ def precompute_host(adj, features, degree, standardize=False, out=None, out_bloc
     n = int(n)
     if features.dim() != 2 or features.shape[0] != n or features.dtype != torch.float32 or features.is_cuda:
         raise ValueError("features must be a host float32 [N, F] tensor with N = %d rows" % n)
-    features = features.contiguous()
+    if features.stride(1) != 1 or (n > 1 and features.stride(0) < features.shape[1]):
+        features = features.contiguous()
     f = int(features.shape[1])
+    fs = int(features.stride(0)) if n > 1 else f          # host row pitch of X in floats (pinned_rows: 64-byte multiples)
     if out is None:
         out = torch.empty((n, f), dtype=torch.float32).pin_memory()
-    if tuple(out.shape) != (n, f) or out.dtype != torch.float32 or not out.is_contiguous() or out.is_cuda:
-        raise ValueError("out must be a contiguous float32 [N, F] host tensor")
+    if tuple(out.shape) != (n, f) or out.dtype != torch.float32 or out.is_cuda or (f > 1 and out.stride(1) != 1) \
+            or (n > 1 and out.stride(0) < f):
+        raise ValueError("out must be a float32 [N, F] host tensor with unit column stride (rows may be padded)")
+    os_ = int(out.stride(0)) if n > 1 else f              # host row pitch of the result
     chunk = default_chunk() if chunk is None else chunk
     if isinstance(col_slab, (list, tuple)):            # explicit slab widths, in processing order
         widths = [int(w) for w in col_slab]
@@ -279,17 +296,20 @@ def precompute_host(adj, features, degree, standardize=False, out=None, out_bloc
 
             def upload_slab(c0, c1):
                 if by_cols:
-                    _ffi.call("sgc_copy_2d", x.data_ptr() + 4 * c0, 4 * ld, features.data_ptr() + 4 * c0, 4 * f,
+                    _ffi.call("sgc_copy_2d", x.data_ptr() + 4 * c0, 4 * ld, features.data_ptr() + 4 * c0, 4 * fs,
                               4 * (c1 - c0), n, c_in.cuda_stream)
-                else:
+                elif fs == f:
                     x.copy_(features, non_blocking=True)       # whole rows: one contiguous transfer
+                else:
+                    _ffi.call("sgc_copy_2d", x.data_ptr(), 4 * x.stride(0), features.data_ptr(), 4 * fs, 4 * f, n,
+                              c_in.cuda_stream)
                 e = torch.cuda.Event()
                 e.record(c_in)
                 x_up.append(e)
                 mark("x[:, %d:%d] up" % (c0, c1), c_in)
 
             nbytes = lambda t: t.numel() * t.element_size()
-            h2d = nbytes(rp_h) + nbytes(features)
+            h2d = nbytes(rp_h) + n * f * 4
             fill = None
             scan_report = {"scan_gave_up": False}
             # under `group` the scan is opt-in: measured neutral to slightly negative (N = 2: 16.3 vs 15.7 ms, N = 8:
@@ -373,11 +393,14 @@ def precompute_host(adj, features, degree, standardize=False, out=None, out_bloc
             c_out.wait_event(done)
             mark("y[%d:%d, %d:%d] computed" % (r0, r1, c0, c1), main)
             if by_cols:
-                _ffi.call("sgc_copy_2d", out.data_ptr() + 4 * (r0 * f + c0), 4 * f,
+                _ffi.call("sgc_copy_2d", out.data_ptr() + 4 * (r0 * os_ + c0), 4 * os_,
                           y.data_ptr() + 4 * (r0 * ld + c0), 4 * ld, 4 * (c1 - c0), r1 - r0, c_out.cuda_stream)
-            else:
+            elif os_ == f:
                 with torch.cuda.stream(c_out):
                     out[r0:r1].copy_(y[r0:r1], non_blocking=True)
+            else:
+                _ffi.call("sgc_copy_2d", out.data_ptr() + 4 * r0 * os_, 4 * os_, y.data_ptr() + 4 * r0 * y.stride(0),
+                          4 * y.stride(0), 4 * f, r1 - r0, c_out.cuda_stream)
             mark("y[%d:%d, %d:%d] down" % (r0, r1, c0, c1), c_out)
 
         for (c0, c1), up in zip(slabs, x_up):

@@ -378,6 +378,16 @@ def test_precompute_host_pipeline(dev, blocks, col_slab):
     a = sp.csr_matrix((host[3].numpy(), host[2].numpy(), host[1].numpy()), shape=(n, n))
     got3 = sgc_b200.precompute_host(a, x_host, 2, standardize=True, out_blocks=blocks, chunk=0, col_slab=col_slab)
     assert np.array_equal(got3.numpy(), want2)
+    # row-padded pinned staging buffers (64-byte row pitch) for X and the result: same bits, padding untouched
+    from sgc_b200.pipeline import pinned_rows
+    xp, op = pinned_rows(n, 77), pinned_rows(n, 77)
+    assert xp.stride(0) == 80 and xp.is_pinned()
+    xp.copy_(x_host)
+    op.fill_(-5.0)
+    whole = torch.as_strided(op, (n, 80), (80, 1))
+    whole[:, 77:] = -9.0
+    got4 = sgc_b200.precompute_host(host, xp, 2, standardize=True, out=op, out_blocks=blocks, chunk=0, col_slab=col_slab)
+    assert got4 is op and np.array_equal(op.numpy(), want2) and bool((whole[:, 77:] == -9.0).all())
 
 
 @pytest.mark.parametrize("col_slab", [None, 32])
