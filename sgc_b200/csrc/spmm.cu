@@ -286,7 +286,7 @@ static int32_t run_hop(const sgc_plan_impl *pl, const sgc_hop_args_t *a, const f
         // 1.66 ms per fused products hop on 8 GPUs); 1 where every row piece is its own store anyway (feature
         // slabs narrower than the row: Reddit shape) -- there a tile is only a scheduling quantum, and 8 tasks per
         // ticket left a row part of 121 k tasks with 4 tickets per warp (1.62 ms per hop against 0.77 ms for the
-        // plain kernel, profiles/r02_grid_n8.log)
+        // plain kernel, profiles/r02_scale_n8_grid2x4_tile8.json)
         const int gpw = 32 / g;
         const bool tiles = p.stage_stride == (int32_t)ldy;
         int tpw = a->push_tile_tasks > 0 ? a->push_tile_tasks : (tiles ? 8 : 1);
