@@ -179,7 +179,7 @@ def _uniform_value_shared(val_h, dev, group, stream=None):
 
 def host_threads():
     """Workers of the host-side scan of the adjacency values (SGC_B200_HOST_THREADS)."""
-    return max(1, int(os.environ.get("SGC_B200_HOST_THREADS", min(8, os.cpu_count() or 1))))
+    return max(1, int(os.environ.get("SGC_B200_HOST_THREADS", min(12, os.cpu_count() or 1))))
 
 
 PCIE_BYTES_PER_US = 40e3        # ~40 GB/s: sustained pinned H2D rate of the strided / contiguous copies
