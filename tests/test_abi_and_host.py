@@ -366,3 +366,36 @@ def test_row_blocks_cover_rows_and_balance_entries():
         assert sum(sizes) == nnz
         if nb <= 8:
             assert max(sizes) <= nnz // nb + 128 * 900                    # within one aligned cut of the target
+
+
+def test_column_block_policy_is_off_unless_asked(monkeypatch):
+    """propagate.col_blocks_for: 0 by default (the column-blocked hop measured slower); an explicit
+    count is taken as is; 'auto' only names block counts for one-slab-wide operands between 2x and 64x the L2 budget."""
+    from sgc_b200 import propagate
+    from sgc_b200.graph import L2_SLAB_BUDGET
+
+    class G(object):
+        def __init__(self, n_cols):
+            self.n_cols = n_cols
+    monkeypatch.delenv("SGC_B200_COL_BLOCKS", raising=False)
+    assert propagate.col_blocks_for(G(2_449_029), 416) == 0
+    monkeypatch.setenv("SGC_B200_COL_BLOCKS", "7")
+    assert propagate.col_blocks_for(G(10), 416) == 7
+    monkeypatch.setenv("SGC_B200_COL_BLOCKS", "auto")
+    nb = propagate.col_blocks_for(G(2_449_029), 416)            # products: X = 1 GB
+    assert nb >= 2 and 2_449_029 * 416 / nb <= L2_SLAB_BUDGET
+    assert propagate.col_blocks_for(G(232_965), 416) == 0        # fits L2 twice over: single pass
+    assert propagate.col_blocks_for(G(232_965), 2432) == 0       # wider than one slab: feature slabs instead
+    assert propagate.col_blocks_for(G(111_059_956), 512) == 0    # papers100M: y would be re-read too often
+
+
+def test_grid_cost_model_is_monotone():
+    from sgc_b200 import dist as sd
+    widths = [sd._block_cost_slabs(w) for w in range(1, 700)]
+    assert all(b >= a for a, b in zip(widths, widths[1:]))        # a wider block never costs less
+    assert sd._block_cost_slabs(128) == 1.0 and sd._block_cost_slabs(256) == 2.0
+    # more row parts: less compute per rank, more pushed bytes per exchanging hop
+    n, nnz, f = 232965, 23.4e6, 602
+    assert sd.grid_cost_ms(n, nnz, f, 1, 1, 8) < sd.grid_cost_ms(n, nnz, f, 1, 1, 4) < sd.grid_cost_ms(n, nnz, f, 1, 1, 2)
+    # feature sharding has no exchange term: K hops cost K times one hop
+    assert abs(sd.grid_cost_ms(n, nnz, f, 3, 8, 1) - 3 * sd.grid_cost_ms(n, nnz, f, 1, 8, 1)) < 1e-9
