@@ -9,6 +9,9 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libsgc_b200.so")
+# A/B builds of the same library (tools/sweep_occupancy.py): SGC_B200_LIB names another in-tree .so
+if os.environ.get("SGC_B200_LIB"):
+    LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), os.path.basename(os.environ["SGC_B200_LIB"]))
 
 c_i32, c_i64, c_u32, c_sz, c_p = (ctypes.c_int32, ctypes.c_int64, ctypes.c_uint32, ctypes.c_size_t,
                                   ctypes.c_void_p)

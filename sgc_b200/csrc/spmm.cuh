@@ -26,6 +26,15 @@
 namespace sgc {
 
 constexpr int HOP_THREADS = 128;
+#ifndef SGC_HOP_MIN_CTAS
+#define SGC_HOP_MIN_CTAS 8      // resident CTAs per SM the plain single-GPU hop kernels are compiled for
+#endif
+// Register cap by variant.  The plain variants (one vector per lane, no fused standardisation) fit 56 registers
+// without spilling and run with 8-9 CTAs per SM instead of 7: Reddit shape K = 2 8.03 -> 7.68 ms, products hop
+// 7.09 -> 6.96 ms, bit-identical (tools/sweep_occupancy.py, profiles/r02_sweep_occupancy.log; 10 CTAs / 48
+// registers: no further gain).  The variants with two vectors per lane or the standardisation in the gather
+// would spill under that cap and keep the looser one.
+template <int U, int STD> constexpr int hop_min_ctas() { return (U == 1 && STD == 0) ? SGC_HOP_MIN_CTAS : 5; }
 constexpr int64_t TICKET_MIN_WORK = 2 * 1000 * 1000;      // gathers per launch above which the ticket grid pays
 
 struct HopDev {
@@ -376,7 +385,7 @@ __device__ __forceinline__ void hop_task(const HopDev &p, const int64_t task, co
 }
 
 template <int G, int VEC, int U, bool FUSED, int STD, bool HOT>
-__global__ void __launch_bounds__(HOP_THREADS, 5)
+__global__ void __launch_bounds__(HOP_THREADS, (hop_min_ctas<U, STD>()))
 spmm_hop_kernel(const HopDev p)
 {
     constexpr int GPW = 32 / G;
@@ -418,7 +427,7 @@ __device__ __forceinline__ void retire_warp(unsigned long long *counters, int la
 
 // The single-GPU hop on a persistent grid: every warp draws tiles of `tpw` x 32/G consecutive tasks.
 template <int G, int VEC, int U, bool FUSED, int STD, bool HOT>
-__global__ void __launch_bounds__(HOP_THREADS, 5)
+__global__ void __launch_bounds__(HOP_THREADS, (hop_min_ctas<U, STD>()))
 spmm_hop_ticket_kernel(const HopDev p, const int64_t n_tiles)
 {
     constexpr int GPW = 32 / G;

@@ -9,7 +9,7 @@ timeout 1500 python -m pytest tests -m gpu -q -x --durations=12 > gpurun_out/pyt
 tail -22 gpurun_out/pytest_gpu.log
 timeout 900 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?" | tee -a gpurun_out/summary_final.txt
 head -c 1200 gpurun_out/bench.json; echo; tail -3 gpurun_out/bench.err
-timeout 300 python tools/e2e_sweep.py > gpurun_out/e2e_sweep.log 2>&1; echo "e2e sweep rc=$?" | tee -a gpurun_out/summary_final.txt
+[ "${SKIP_EXTRAS:-0}" = 1 ] || timeout 300 python tools/e2e_sweep.py > gpurun_out/e2e_sweep.log 2>&1; echo "e2e sweep rc=$?" | tee -a gpurun_out/summary_final.txt
 grep -v "Warn\|warn" gpurun_out/e2e_sweep.log | tail -36
 CMD="python bench.py --steps 3 --warmup 3 --no-cpu-baseline --skip-e2e --skip-incumbent --skip-variants --workload reddit"
 $CMD > gpurun_out/bench_short.json 2> gpurun_out/bench_short.err && \
@@ -20,6 +20,6 @@ for shape in reddit products; do
   ncu -i gpurun_out/hop_$shape.ncu-rep --page raw --csv 2>/dev/null | python tools/ncu_select.py > gpurun_out/hop_${shape}_sel.csv
   cat gpurun_out/hop_${shape}_sel.csv
 done
-timeout 400 python bench.py --impl reference > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "ref rc=$?" | tee -a gpurun_out/summary_final.txt
+[ "${SKIP_EXTRAS:-0}" = 1 ] || timeout 400 python bench.py --impl reference > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "ref rc=$?" | tee -a gpurun_out/summary_final.txt
 head -c 600 gpurun_out/bench_ref.json; echo
 cat gpurun_out/summary_final.txt
