@@ -470,8 +470,11 @@ spmm_hop_ticket_kernel(const HopDev p, const int64_t n_tiles)
 // (wait_group.read 1).  Before the warp exits every lane waits for full COMPLETION of its stores
 // (cp.async.bulk.wait_group 0, not .read): the writes have been performed at the peers when the grid
 // completes, and the stream-ordered barrier that follows the kernel (dist.py) publishes them.
+#ifndef SGC_PEERS_MIN_CTAS
+#define SGC_PEERS_MIN_CTAS 6
+#endif
 template <int G, int VEC, int U, bool FUSED, bool HOT>
-__global__ void __launch_bounds__(HOP_THREADS, 6)
+__global__ void __launch_bounds__(HOP_THREADS, SGC_PEERS_MIN_CTAS)
 spmm_hop_peers_kernel(const HopDev p, const int64_t n_tiles)
 {
     constexpr int GPW = 32 / G;
