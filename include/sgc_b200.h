@@ -278,9 +278,9 @@ typedef struct sgc_hop_args {
      * sgc_ipc_open() and reached over NVLink.  peer_y_d[p] corresponds to y_d (same logical row
      * 0, same leading dimension ldy).  n_peers = 0 for a single-GPU hop. */
     int32_t       n_peers;
-    int32_t       push_tile_tasks; /* consecutive tasks per group slot a warp draws per ticket (0 = default: 8
-                                      with peers, else 2-4); with peers their rows travel as ONE bulk store
-                                      when they are contiguous in y; rows per tile <= 32                  */
+    int32_t       push_tile_tasks; /* consecutive tasks per group slot a warp draws per ticket (0 = default:
+                                      with peers 4 where the rows of a tile are contiguous in y and travel
+                                      as ONE bulk store, else 1; without peers 1-4); rows per tile <= 32 */
     float        *peer_y_d[SGC_MAX_PEERS];
     /* Optional halo mask, one uint32 per row of this hop (n_rows entries): bit p set = peer p's
      * shard gathers this row in the next hop, so it must be pushed to peer_y_d[p]; clear = peer p

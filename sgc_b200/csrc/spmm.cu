@@ -281,15 +281,17 @@ static int32_t run_hop(const sgc_plan_impl *pl, const sgc_hop_args_t *a, const f
                     "(the bulk stores cover the pad columns)");
         // tiles are contiguous in y when one slab covers the whole padded row
         p.stage_stride = (p.n_slabs == 1 && ldy <= slab && y_vec == 4) ? (int32_t)ldy : slab;
-        // rows per tile: push_tile_tasks tasks per group slot, at most 32 rows per warp tile.  Default: 8 where a
-        // tile can leave as ONE bulk store (rows contiguous in the operand: bigger NVLink transactions, 1.53 vs
-        // 1.66 ms per fused products hop on 8 GPUs); 1 where every row piece is its own store anyway (feature
+        // rows per tile: push_tile_tasks tasks per group slot, at most 32 rows per warp tile.  Default: 4 where a
+        // tile can leave as ONE bulk store (rows contiguous in the operand: bigger NVLink transactions -- fused
+        // products hop on 8 GPUs 1.66 ms with single rows, 1.57 with 2, 1.52 with 4, 1.53 with 8, 1.87 with 16 --
+        // and half the staging memory of 8, which comes out of L1: compute side 4.10 -> 3.98 ms on a half of the
+        // rows, profiles/r02_sweep_peer_tiles_1gpu.log); 1 where every row piece is its own store anyway (feature
         // slabs narrower than the row: Reddit shape) -- there a tile is only a scheduling quantum, and 8 tasks per
         // ticket left a row part of 121 k tasks with 4 tickets per warp (1.62 ms per hop against 0.77 ms for the
         // plain kernel, profiles/r02_scale_n8_grid2x4_tile8.json)
         const int gpw = 32 / g;
         const bool tiles = p.stage_stride == (int32_t)ldy;
-        int tpw = a->push_tile_tasks > 0 ? a->push_tile_tasks : (tiles ? 8 : 1);
+        int tpw = a->push_tile_tasks > 0 ? a->push_tile_tasks : (tiles ? 4 : 1);
         if (tpw * gpw > 32) tpw = 32 / gpw;
         p.tpw = tpw;
         SGC_REQUIRE(pl->tile_counter != nullptr, "spmm_hop: the plan has no workspace (needed by the peer variant)");

@@ -76,7 +76,7 @@ def as_graph(adj):
 
 
 def push_tile_tasks():
-    """Rows of a peer tile per group slot (SGC_B200_PUSH_ROWS; 0 = the library default of 8): consecutive
+    """Rows of a peer tile per group slot (SGC_B200_PUSH_ROWS; 0 = the library default: 4 where a tile leaves as one bulk store, else 1): consecutive
     output rows that travel to a peer as ONE cp.async.bulk store when they are contiguous in the operand."""
     return int(_ENV("SGC_B200_PUSH_ROWS", "0"))
 
