@@ -188,6 +188,34 @@ int32_t sgc_col_stats(const float *x_d, int64_t n, int64_t f, int64_t ld, float 
                       float *std32_d, double *mean64_d, double *std64_d, void *ws_d,
                       size_t ws_bytes, void *stream);
 
+/* sgc_col_stats without a workspace argument.  (No counterpart in the reference: this exists
+ * for hosts of the library, not for a reference call site.)
+ *
+ * Who needs it: callers that have no way to obtain device scratch -- code running where
+ * cudaMalloc is off limits (inside another runtime's callback, or under a policy that gives the
+ * whole device to an allocator the caller does not own), and loops that cannot afford the
+ * device-wide synchronisation an allocation may imply.  They still pass x and the output
+ * vectors; the per-block partial sums go to a static __device__ array inside the library.
+ * This call performs no cudaMalloc/cudaFree and calls no allocating library routine.
+ *
+ * Limit: the partial sums take 16 * f * min(ceil(n/64), 4 * SM count) bytes and must fit in
+ * SGC_COL_STATS_STATIC_MAX_BYTES (8 MiB); on a 148-SM B200 that is any n with f <= 885, and
+ * wider matrices only below about 37,800 rows.  Beyond it the call returns SGC_ERR_WORKSPACE and touches nothing.
+ * The 8 MiB are resident on every GPU that loads the library, until the process exits.
+ *
+ * First call on each device: looks up the array's device address (cudaGetSymbolAddress, with
+ * that device current) and caches it.  Make that first call outside any stream capture.
+ *
+ * Sharing: all calls on a device use the same array.  Nothing in it needs clearing between
+ * calls (each call overwrites every partial sum it later reads), but two calls whose kernels
+ * can run at the same time on one GPU -- different streams, or different host threads -- race
+ * on it and both results are garbage.  Order them on one stream, or with events.
+ *
+ * Results are bit-identical to sgc_col_stats on the same input (same blocks, same order). */
+#define SGC_COL_STATS_STATIC_MAX_BYTES (8u << 20)
+int32_t sgc_col_stats_static(const float *x_d, int64_t n, int64_t f, int64_t ld, float *mean32_d,
+                             float *std32_d, double *mean64_d, double *std64_d, void *stream);
+
 /* x <- (x - mean[c]) / std[c] in place, the fp32 expression of utils.py:119 evaluated exactly
  * (one subtraction, one IEEE division per element).  x_d: fp32 [n, ld] row-major. */
 int32_t sgc_standardize_inplace(float *x_d, int64_t n, int64_t f, int64_t ld, const float *mean_d,

@@ -71,6 +71,7 @@ SIGNATURES = {
     "sgc_coo_to_csr": (c_i32, [c_i64, c_i64, c_p, c_p, c_p, c_p, c_p, c_p]),
     "sgc_col_stats_workspace_bytes": (c_sz, [c_i64, c_i64]),
     "sgc_col_stats": (c_i32, [c_p, c_i64, c_i64, c_i64, c_p, c_p, c_p, c_p, c_p, c_sz, c_p]),
+    "sgc_col_stats_static": (c_i32, [c_p, c_i64, c_i64, c_i64, c_p, c_p, c_p, c_p, c_p]),
     "sgc_standardize_inplace": (c_i32, [c_p, c_i64, c_i64, c_i64, c_p, c_p, c_p]),
     "sgc_spmm_plan_workspace_bytes": (c_sz, [c_i64, c_i64, c_i32]),
     "sgc_spmm_plan_create": (c_i32, [c_i64, c_i64, c_i64, c_p, c_p, c_i32, c_p, c_sz,

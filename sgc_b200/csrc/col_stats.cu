@@ -9,6 +9,8 @@
 // block order by a second kernel (deterministic; no atomics).  HBM-bound: reads 4*n*f bytes once.
 #include "common.cuh"
 
+#include <mutex>
+
 namespace sgc {
 
 constexpr int CS_THREADS = 256;
@@ -114,6 +116,43 @@ static int stats_blocks(int64_t n)
 
 using namespace sgc;
 
+// ---- the same statistics for callers that must not allocate ---------------------------------
+//
+// sgc_col_stats needs a few MB of device scratch for its per-block partial sums, and the caller
+// has to get that from somewhere.  Some callers cannot: a plugin called back from inside another
+// framework's op or stream callback where cudaMalloc is forbidden, a process whose whole device
+// budget was handed to a pool it does not own, or a real-time loop where cudaMalloc's implicit
+// device synchronisation is not acceptable.  For them the partial sums live in the array below,
+// which is part of the library image: every GPU on which the library's module is loaded carries
+// these 8 MiB from then until the process exits, used or not.
+//
+// Host code must not treat `cs_static_scratch` as a pointer: on the host that name is only a
+// handle for the symbol.  static_scratch_ptr() asks the runtime for the real device address,
+// once per device and with that device current, and the kernels are handed that address.
+constexpr size_t CS_STATIC_DOUBLES = SGC_COL_STATS_STATIC_MAX_BYTES / sizeof(double);
+static __device__ __align__(256) double cs_static_scratch[CS_STATIC_DOUBLES];
+
+constexpr int CS_MAX_DEVICES = 64;
+static std::mutex cs_static_mutex;
+static double *cs_static_addr[CS_MAX_DEVICES];     // device address of the array, per device ordinal
+
+// Device address of cs_static_scratch on the current device (cached after the first call there).
+static int32_t static_scratch_ptr(double **out)
+{
+    int dev = -1;
+    SGC_CUDA_TRY(cudaGetDevice(&dev));
+    SGC_REQUIRE(dev >= 0 && dev < CS_MAX_DEVICES, "col_stats_static: device ordinal %d out of range", dev);
+    std::lock_guard<std::mutex> lock(cs_static_mutex);
+    if (!cs_static_addr[dev]) {
+        double *p = nullptr;
+        SGC_CUDA_TRY(cudaGetSymbolAddress(reinterpret_cast<void **>(&p), cs_static_scratch));
+        SGC_REQUIRE(p != nullptr, "col_stats_static: cudaGetSymbolAddress returned a null address");
+        cs_static_addr[dev] = p;
+    }
+    *out = cs_static_addr[dev];
+    return SGC_OK;
+}
+
 extern "C" {
 
 size_t sgc_col_stats_workspace_bytes(int64_t n, int64_t f)
@@ -136,6 +175,38 @@ int32_t sgc_col_stats(const float *x_d, int64_t n, int64_t f, int64_t ld, float 
     const int64_t rows_per_block = ceil_div(n, nb);
     const unsigned tiles = (unsigned)ceil_div(f, CS_THREADS);
     double *part = reinterpret_cast<double *>(ws_d);
+    col_stats_partial_kernel<<<dim3((unsigned)nb, tiles), CS_THREADS, 0, s>>>(x_d, n, f, ld, rows_per_block, part);
+    SGC_LAUNCH_CHECK();
+    col_stats_final_kernel<<<tiles, CS_THREADS, 0, s>>>(x_d, n, f, nb, part, mean32_d, std32_d, mean64_d, std64_d);
+    SGC_LAUNCH_CHECK();
+    return SGC_OK;
+}
+
+// Column statistics with the partial sums in the library's own static array; see the block
+// comment above cs_static_scratch and the declaration in include/sgc_b200.h.
+int32_t sgc_col_stats_static(const float *x_d, int64_t n, int64_t f, int64_t ld, float *mean32_d,
+                             float *std32_d, double *mean64_d, double *std64_d, void *stream)
+{
+    SGC_REQUIRE(x_d && n >= 1 && f >= 1 && ld >= f, "col_stats_static: bad arguments (n=%lld f=%lld ld=%lld)",
+                (long long)n, (long long)f, (long long)ld);
+    // same block count as sgc_col_stats, so the partial sums are added in the same order and the
+    // two entry points agree bit for bit
+    const int nb = stats_blocks(n);
+    const size_t need = (size_t)nb * 2 * (size_t)f * sizeof(double);
+    if (need > SGC_COL_STATS_STATIC_MAX_BYTES) {
+        set_error("col_stats_static: n=%lld f=%lld needs %zu bytes of partial sums, the built-in scratch holds "
+                  "%zu; use sgc_col_stats with a caller-provided workspace",
+                  (long long)n, (long long)f, need, (size_t)SGC_COL_STATS_STATIC_MAX_BYTES);
+        return SGC_ERR_WORKSPACE;
+    }
+    double *part = nullptr;
+    const int32_t rc = static_scratch_ptr(&part);
+    if (rc != SGC_OK) return rc;
+    cudaStream_t s = as_stream(stream);
+    const int64_t rows_per_block = ceil_div(n, nb);
+    const unsigned tiles = (unsigned)ceil_div(f, CS_THREADS);
+    // Nothing in the array has to start at zero: the first kernel writes every partial sum the
+    // second one reads (nb blocks x 2 x f columns), so whatever the previous call left is dead.
     col_stats_partial_kernel<<<dim3((unsigned)nb, tiles), CS_THREADS, 0, s>>>(x_d, n, f, ld, rows_per_block, part);
     SGC_LAUNCH_CHECK();
     col_stats_final_kernel<<<tiles, CS_THREADS, 0, s>>>(x_d, n, f, nb, part, mean32_d, std32_d, mean64_d, std64_d);
