@@ -122,7 +122,10 @@ class SgcGraph(object):
         blocks together hold one more copy of col / sval plus n_blocks row-pointer arrays).  Entries of a row
         keep their ascending order inside every block, which is what lets `propagate.hop_col_blocked` continue
         each row's FMA chain block by block.  Cached per n_blocks.  Each block reports `n_cols` = the number of
-        rows of X it gathers from, so that the hop sizes its L2 policy for the block, not for all of X."""
+        rows of X it gathers from, so that the hop sizes its L2 policy for the block, not for all of X.
+        Row-slice views (pipeline.row_blocks, the sharded propagator's sub-graphs) keep absolute offsets in
+        `row_ptr` and share the parent's `col` array: only the entries [row_ptr[0], row_ptr[-1]) are theirs, and
+        the blocks are built from that range alone (one small D2H read of the two offsets)."""
         n_blocks = max(1, min(int(n_blocks), max(self.n_cols, 1)))
         hit = self._plans.get(("col_blocks", n_blocks))
         if hit is not None:
@@ -132,9 +135,12 @@ class SgcGraph(object):
         per = (self.n_cols + n_blocks - 1) // n_blocks
         per = (per + 127) // 128 * 128
         with torch.cuda.device(dev):
-            rows = torch.empty(self.nnz, dtype=torch.int32, device=dev)
-            _ffi.call("sgc_csr_expand_rows", self.n_rows, _ffi.ptr(self.row_ptr), 0, _ffi.ptr(rows), stream_ptr())
-            blk = torch.div(self.col, per, rounding_mode="floor")
+            b, e = (int(v) for v in self.row_ptr[[0, -1]].cpu().tolist())
+            row_ptr = self.row_ptr if b == 0 else (self.row_ptr - b).contiguous()
+            col, sval = self.col[b:e], sval[b:e]
+            rows = torch.empty(e - b, dtype=torch.int32, device=dev)
+            _ffi.call("sgc_csr_expand_rows", self.n_rows, _ffi.ptr(row_ptr), 0, _ffi.ptr(rows), stream_ptr())
+            blk = torch.div(col, per, rounding_mode="floor")
             out = []
             for b in range(n_blocks):
                 c0, c1 = b * per, min((b + 1) * per, self.n_cols)
@@ -144,7 +150,7 @@ class SgcGraph(object):
                 counts = torch.bincount(rows[keep].long(), minlength=self.n_rows)
                 rp = torch.zeros(self.n_rows + 1, dtype=torch.int64, device=dev)
                 torch.cumsum(counts, 0, out=rp[1:])
-                g = SgcGraph(self.n_rows, c1 - c0, rp, self.col[keep].contiguous(), None, None,
+                g = SgcGraph(self.n_rows, c1 - c0, rp, col[keep].contiguous(), None, None,
                              sval=sval[keep].contiguous())
                 out.append((c0, c1, g))
         self._plans[("col_blocks", n_blocks)] = out
