@@ -28,7 +28,25 @@ __device__ __forceinline__ float4 ld_hint_v4(const float4 *p, uint64_t pol)
     return r;
 }
 
-// pattern bit 0: 0 = pieces in address order (grid-stride), 1 = pieces in a hashed order (the gather's);
+// A permutation of [0, n): odd multiply + constant, xor-shift and odd multiply are each invertible modulo
+// 2^bits (the smallest power of two >= n), and values that land in [n, 2^bits) are walked round the cycle until
+// they fall inside (fewer than two steps on average).  Every piece is therefore read exactly once per repetition
+// -- the working set is the whole buffer and the byte count bytes-per-rep is exact.
+__device__ __forceinline__ int64_t permute_piece(uint64_t p, uint64_t n, int bits, uint64_t salt)
+{
+    const uint64_t mask = (bits >= 64) ? ~0ull : ((1ull << bits) - 1ull);
+    const int sh = bits / 2 > 0 ? bits / 2 : 1;
+    do {
+        p = (p * 0x9E3779B97F4A7C15ull + salt) & mask;
+        p ^= p >> sh;
+        p = (p * 0xD1B54A32D192ED03ull) & mask;
+        p ^= p >> sh;
+    } while (p >= n);
+    return (int64_t)p;
+}
+
+// pattern bit 0: 0 = pieces in address order (grid-stride), 1 = pieces in a pseudo-random order without
+// repetition (the gather's: a permutation of the pieces, new for every repetition);
 // pattern bit 1: 0 = L1::no_allocate loads, 1 = the hop kernel's own load (L1-allocating, L2 evict_last hint).
 __global__ void __launch_bounds__(PROBE_THREADS)
 l2_read_probe_kernel(const float4 *__restrict__ buf, int64_t n_pieces, int64_t stride_v4, int32_t reps,
@@ -41,18 +59,19 @@ l2_read_probe_kernel(const float4 *__restrict__ buf, int64_t n_pieces, int64_t s
     uint64_t pol;
     asm("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
     const bool hashed = (pattern & 1) != 0, alloc = (pattern & 2) != 0;
+    int bits = 1;
+    while (bits < 63 && (1ll << bits) < n_pieces) ++bits;
     for (int r = 0; r < reps; ++r) {
         for (int64_t p0 = warp; p0 < n_pieces; p0 += n_warps * PROBE_UNROLL) {
             float4 v[PROBE_UNROLL];
 #pragma unroll
             for (int u = 0; u < PROBE_UNROLL; ++u) {
                 int64_t p = p0 + (int64_t)u * n_warps;
-                if (p >= n_pieces) p = warp;
-                if (hashed) {
-                    uint64_t z = (uint64_t)p * 0x9E3779B97F4A7C15ull + (uint64_t)r * 0xD1B54A32D192ED03ull;
-                    z ^= z >> 29;
-                    p = (int64_t)(((z >> 32) * (uint64_t)n_pieces) >> 32);      // n_pieces < 2^32
+                if (p >= n_pieces) {                        // tail of the last round: nothing to read, nothing counted
+                    v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    continue;
                 }
+                if (hashed) p = permute_piece((uint64_t)p, (uint64_t)n_pieces, bits, (uint64_t)r * 0xD1B54A32D192ED03ull);
                 v[u] = alloc ? ld_hint_v4(buf + p * stride_v4 + lane, pol) : ld_l2_v4(buf + p * stride_v4 + lane);
             }
 #pragma unroll
