@@ -273,11 +273,11 @@ def _push_breakdown(prop, k_hops, dev, reps=5):
     h = default_hints()
     res = {
         "hop_without_pushes_ms": timed(lambda: hop(sg.graph, src[:, :f], out=out, peers=peers, peer_mask=prop.peer_mask,
-                                                   hints=h | 8, pad_owned=True)),
+                                                   hints=h | 8, pad_owned=True, pitch_owned=True)),
         "fused_hop_ms": timed(lambda: hop(sg.graph, src[:, :f], out=out, peers=peers, peer_mask=prop.peer_mask,
-                                          pad_owned=True)),
+                                          pad_owned=True, pitch_owned=True)),
         "fused_hop_row_stores_ms": timed(lambda: hop(sg.graph, src[:, :f], out=out, peers=peers, peer_mask=prop.peer_mask,
-                                                     hints=h | 32, pad_owned=True)),
+                                                     hints=h | 32, pad_owned=True, pitch_owned=True)),
         "last_hop_ms": timed(lambda: hop(sg.graph, src[:, :f], out=out, pad_owned=True)),
         "barrier_ms": timed(prop._barrier),
     }

@@ -60,7 +60,8 @@ int32_t sgc_l2_set_persisting_bytes(int64_t bytes, int64_t *granted_out);
 /* Measurement aid (bench.py `roofline.l2`, tools/l2_peak.py): reads the `bytes` (multiple of 512) at buf_d
  * `reps` times from all SMs in 512-byte pieces (32 lanes x 16 bytes, the hop kernel's gather shape) with L1
  * allocation off -- with a buffer that stays resident in the 126 MB L2 the CUDA-event time of this launch is
- * the L2 -> SM read bandwidth of the box.  pattern bit 0: pieces in address order / hashed order (the gather's);
+ * the L2 -> SM read bandwidth of the box.  pattern bit 0: pieces in address order / in a pseudo-random
+ * permutation, new per repetition (the gather's access order; every piece is read exactly once per repetition);
  * bit 1: L1::no_allocate loads / the hop kernel's own load flavour (L1-allocating, L2 evict_last hint).
  * piece_stride_bytes: distance between pieces (0 = 512, contiguous; 2432 = one 128-float slab of 608-float rows:
  * the Reddit-shaped hop's footprint -- bytes then spans the strided range, of which 512/stride is read).  sink_d: one
@@ -233,8 +234,10 @@ typedef struct sgc_plan sgc_plan_t;
 size_t  sgc_spmm_plan_workspace_bytes(int64_t n_rows, int64_t nnz, int32_t chunk);
 /* Builds the split table on `stream`; SYNCHRONISES the stream once to read back the item count.
  * The plan keeps pointers into ws_d and to row_ptr_d/col_d: they must outlive the plan.  The first 256 bytes
- * of ws_d hold the ticket counters of the persistent hop grids (zeroed here; every launch leaves them zero):
- * a plan serves ONE hop at a time -- hops that may run concurrently on different streams need their own plans. */
+ * of ws_d hold 16 pairs of ticket counters for the persistent hop grids: each ticket-scheduled launch takes the
+ * next pair in turn and clears it on its own stream before the kernel, so up to 16 hops on one plan may be in
+ * flight on different streams, and a launch that was aborted mid-run leaves nothing behind for later ones.
+ * (The split-row scratch `partial_d` is the caller's: concurrent hops need one each.) */
 int32_t sgc_spmm_plan_create(int64_t n_rows, int64_t n_cols, int64_t nnz,
                              const int64_t *row_ptr_d, const int32_t *col_d, int32_t chunk,
                              void *ws_d, size_t ws_bytes, sgc_plan_t **plan_out, void *stream);
@@ -265,6 +268,13 @@ int32_t sgc_spmm_plan_tag_hot(sgc_plan_t *plan, int64_t hot_rows, int32_t *col_t
                                      them with whole-vector stores (they receive zeros when the pad columns
                                      of x are zero).  Without the flag nothing beyond column f-1 is written,
                                      so y_d may be a column view of a wider live matrix.                */
+#define SGC_HOP_PITCH_OWNED 32u   /* stronger than PAD_OWNED (and implies it): ALL of columns [f, ldy) of y_d and
+                                     of every peer_y_d are padding of the operand, i.e. y_d / peer_y_d are whole
+                                     padded rows and not column views.  Only then may the peer variant send a
+                                     tile of consecutive rows as ONE bulk store of rows*ldy floats (which
+                                     zero-fills [f, ldy) on the peers).  Without it every pushed row is its own
+                                     store of round_up(f, 4) floats (f floats when f % 4 == 0) and nothing
+                                     else of the peers' rows is touched.                                */
 #define SGC_HOP_ACCUMULATE  16u   /* y_d += S_b x instead of y_d = S x: the plan describes ONE BLOCK OF COLUMNS
                                      of S (a CSR holding only the entries whose column lies in the block) and
                                      every row continues its running sum from the value y_d holds -- same
@@ -299,7 +309,8 @@ typedef struct sgc_hop_args {
                                   rows of a tile into one bulk store, bit6 end the kernel after the
                                   source reads of the bulk stores instead of their completion;
                                   bit7: one warp per task in a one-shot grid instead of the persistent,
-                                  ticket-scheduled grid (A/B measurements)                        */
+                                  ticket-scheduled grid (A/B measurements); bit8: ticket grid even where
+                                  the one-shot grid would be chosen by task count (A/B measurements) */
     /* Row-sharded multi-GPU hop (K5): every output row is ALSO stored, from the registers of the
      * SpMM epilogue, to the same (row, column) offset of n_peers other buffers -- the peers'
      * copies of the gathered operand of the next hop, mapped into this process with

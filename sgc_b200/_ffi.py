@@ -21,6 +21,7 @@ HOP_STD_DIV = 2
 HOP_STD_RCP = 4
 HOP_PAD_OWNED = 8
 HOP_ACCUMULATE = 16
+HOP_PITCH_OWNED = 32
 MAX_PEERS = 15
 IPC_HANDLE_BYTES = 64
 

@@ -248,7 +248,8 @@ static int32_t run_hop(const sgc_plan_impl *pl, const sgc_hop_args_t *a, const f
     p.work = pl->nnz * (int64_t)p.n_slabs;
     p.y_vec = y_vec;
     // whole-vector stores may spill into columns [f, round4(f)) only when the caller owns them as padding
-    const bool pad_owned = (flags & SGC_HOP_PAD_OWNED) != 0 && (a->f + 3) / 4 * 4 <= ldy;
+    const bool pitch_owned = (flags & SGC_HOP_PITCH_OWNED) != 0;      // [f, ldy) is padding: y is not a column view
+    const bool pad_owned = (flags & (SGC_HOP_PAD_OWNED | SGC_HOP_PITCH_OWNED)) != 0 && (a->f + 3) / 4 * 4 <= ldy;
     p.f_store = pad_owned ? (a->f + 3) / 4 * 4 : a->f;
     p.accumulate = (flags & SGC_HOP_ACCUMULATE) ? 1 : 0;
     SGC_REQUIRE(!p.accumulate || (!peers_on && stdmode == 0),
@@ -270,7 +271,10 @@ static int32_t run_hop(const sgc_plan_impl *pl, const sgc_hop_args_t *a, const f
     }
     // ticket-scheduled persistent grid unless the plan has no counters or the caller asks for the one-shot grid
     // (hints bit 7, A/B measurements)
-    p.tile_counter = (a->hints & 128) ? nullptr : pl->tile_counter;
+    // (the pair of counters this launch owns: see TICKET_SLOTS)
+    unsigned long long *const tickets = pl->tile_counter
+        ? pl->tile_counter + 2 * (pl->ticket_seq.fetch_add(1, std::memory_order_relaxed) % TICKET_SLOTS) : nullptr;
+    p.tile_counter = (a->hints & 128) ? nullptr : tickets;
     // tasks per ticket, measured on B200 (profiles/r02_sweep_persistent.log): Reddit shape (5 slabs) 3.89 ms with
     // 1, 4.05 with 2, 4.26 with 4; products shape (whole rows) 7.51 / 7.39 / 7.38 ms
     p.tpw = a->push_tile_tasks > 0 ? a->push_tile_tasks : (p.n_slabs > 1 ? 1 : 4);
@@ -279,8 +283,10 @@ static int32_t run_hop(const sgc_plan_impl *pl, const sgc_hop_args_t *a, const f
         SGC_REQUIRE(y_vec != 4 || a->f % 4 == 0 || pad_owned,
                     "spmm_hop: peer pushes of a width that is not a multiple of 4 floats need SGC_HOP_PAD_OWNED "
                     "(the bulk stores cover the pad columns)");
-        // tiles are contiguous in y when one slab covers the whole padded row
-        p.stage_stride = (p.n_slabs == 1 && ldy <= slab && y_vec == 4) ? (int32_t)ldy : slab;
+        // tiles are contiguous in y when one slab covers the whole padded row; a tile store covers the columns
+        // [f, ldy) of every row on the peers, so the caller must have declared them padding (PITCH_OWNED) --
+        // otherwise rows leave one by one and only round4(f) floats of each are written
+        p.stage_stride = (pitch_owned && p.n_slabs == 1 && ldy <= slab && y_vec == 4) ? (int32_t)ldy : slab;
         // rows per tile: push_tile_tasks tasks per group slot, at most 32 rows per warp tile.  Default: 4 where a
         // tile can leave as ONE bulk store (rows contiguous in the operand: bigger NVLink transactions -- fused
         // products hop on 8 GPUs 1.66 ms with single rows, 1.57 with 2, 1.52 with 4, 1.53 with 8, 1.87 with 16 --
@@ -295,7 +301,7 @@ static int32_t run_hop(const sgc_plan_impl *pl, const sgc_hop_args_t *a, const f
         if (tpw * gpw > 32) tpw = 32 / gpw;
         p.tpw = tpw;
         SGC_REQUIRE(pl->tile_counter != nullptr, "spmm_hop: the plan has no workspace (needed by the peer variant)");
-        p.tile_counter = pl->tile_counter;
+        p.tile_counter = tickets;
     }
     const int64_t n_tasks = (int64_t)p.n_slabs * (p.n_long_items + p.n_rows);
     int32_t rc = fn(p, n_tasks, s);

@@ -22,6 +22,7 @@
 // value in registers.
 #pragma once
 #include "common.cuh"
+#include <atomic>
 
 namespace sgc {
 
@@ -75,6 +76,11 @@ struct HopDev {
     const uint32_t *peer_mask;   // per-row bit set of peers that need the row (null: all)
 };
 
+// The first 256 bytes of a plan workspace hold 16 independent ticket-counter pairs.  Every ticket-scheduled launch
+// takes the next pair in turn and clears it on its stream first, so hops on one plan from different streams do
+// not share counters (up to 16 in flight), and a launch that died mid-run cannot leave stale tickets behind.
+constexpr int TICKET_SLOTS = 16;
+
 struct sgc_plan_impl {
     int64_t n_rows, n_cols, nnz;
     const int64_t *row_ptr;
@@ -87,7 +93,8 @@ struct sgc_plan_impl {
     const int32_t *lr_row;
     const int64_t *lr_first;
     const int32_t *lr_cnt;
-    unsigned long long *tile_counter;   // 8 bytes at the head of the plan workspace (peer variant's tickets)
+    unsigned long long *tile_counter;   // head of the plan workspace: TICKET_SLOTS pairs (next ticket, retired warps)
+    mutable std::atomic<uint32_t> ticket_seq{0};   // launches so far: launch i uses pair i % TICKET_SLOTS
     const int32_t *col_tagged;   // col with bit 31 set on "hot" columns (sgc_spmm_plan_tag_hot), or null
     int64_t n_hot_cols;
     int32_t hot_threshold;
@@ -623,6 +630,7 @@ int32_t launch_hop(const HopDev &p, int64_t n_tasks, cudaStream_t s)
         }
         const int64_t want = ceil_div(n_tiles, HOP_THREADS / 32);
         const int64_t cap = (int64_t)sm_count() * occ;
+        SGC_CUDA_TRY(cudaMemsetAsync(p.tile_counter, 0, 2 * sizeof(unsigned long long), s));
         kern<<<(unsigned)(want < cap ? want : cap), HOP_THREADS, smem, s>>>(p, n_tiles);
         SGC_LAUNCH_CHECK();
         return SGC_OK;
@@ -641,6 +649,7 @@ int32_t launch_hop(const HopDev &p, int64_t n_tasks, cudaStream_t s)
                 const int RT = p.tpw * GPW;
                 const int64_t n_tiles = ceil_div(n_tasks, RT);
                 const int64_t want = ceil_div(n_tiles, HOP_THREADS / 32);
+                SGC_CUDA_TRY(cudaMemsetAsync(p.tile_counter, 0, 2 * sizeof(unsigned long long), s));
                 kern<<<(unsigned)(want < cap ? want : cap), HOP_THREADS, 0, s>>>(p, n_tiles);
                 SGC_LAUNCH_CHECK();
                 return SGC_OK;

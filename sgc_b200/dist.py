@@ -96,7 +96,7 @@ def default_mode(device):
 def _cuda_hop(graph, x, out, peers=None, peer_mask=None):
     from .propagate import hop
     # `out` is always a row range of a full-height padded operand (ld = pad_ld(f), pad columns zero)
-    hop(graph, x, out=out, peers=peers, peer_mask=peer_mask, pad_owned=True)
+    hop(graph, x, out=out, peers=peers, peer_mask=peer_mask, pad_owned=True, pitch_owned=bool(peers))
 
 
 def halo_enabled():
@@ -161,6 +161,7 @@ class SymmetricBuffer(object):
     def __init__(self, rows, ld, device, group=None):
         lib = _ffi.lib()
         self.rows, self.ld, self.group = int(rows), int(ld), group
+        self.device = torch.device(device)
         self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
         nbytes = self.rows * self.ld * 4
         with torch.cuda.device(device):
@@ -197,13 +198,19 @@ class SymmetricBuffer(object):
         if self._state["closed"]:
             return
         self.tensor = None
-        self._state["closed"] = True
         lib = _ffi.lib()
-        torch.cuda.synchronize()
-        for ptr in self._opened:
-            lib.sgc_ipc_close(ptr)
-        dist.barrier(group=self.group)
-        lib.sgc_symm_free(self._local)
+        try:
+            with torch.cuda.device(self.device):
+                torch.cuda.synchronize(self.device)           # this buffer's GPU, whatever the current device is
+                while self._opened:                           # emptied as it goes: the finaliser shares this list
+                    lib.sgc_ipc_close(self._opened.pop())
+                dist.barrier(group=self.group)
+        finally:
+            # also when the rendezvous failed (a peer died or timed out): the local allocation is still freed,
+            # and only now does the finaliser of last resort have nothing left to do
+            with torch.cuda.device(self.device):
+                lib.sgc_symm_free(self._local)
+            self._state["closed"] = True
 
 
 class ShardedPropagator(object):

@@ -82,7 +82,7 @@ def push_tile_tasks():
 
 
 def _hop_args(g, plan, x, ldx, y, ldy, f, partial, mean, std, std_mode, slab, hints, peers=None, peer_mask=None,
-              pad_owned=False):
+              pad_owned=False, pitch_owned=False):
     a = _ffi.HopArgs()
     use_fused = g.fused and fused_norm()
     if g.fused and not use_fused:
@@ -97,6 +97,8 @@ def _hop_args(g, plan, x, ldx, y, ldy, f, partial, mean, std, std_mode, slab, hi
             a.peer_mask_d = _ffi.ptr(peer_mask)
     a.push_tile_tasks = push_tile_tasks()
     flags = _ffi.HOP_PAD_OWNED if pad_owned else 0
+    if pitch_owned:
+        flags |= _ffi.HOP_PITCH_OWNED
     if use_fused:
         flags |= _ffi.HOP_FUSED_NORM
         a.aval_d, a.dinv_d, a.dinv_rows_d = _ffi.ptr(g.aval), _ffi.ptr(g.dinv), _ffi.ptr(g.dinv_rows)
@@ -188,7 +190,7 @@ def hop_col_blocked(g, x, n_blocks, chunk=None, hints=None, out=None, pad_owned=
 
 
 def hop(adj, x, mean=None, std=None, chunk=None, slab=None, hints=None, std_mode=None, out=None, peers=None,
-        peer_mask=None, pad_owned=False):
+        peer_mask=None, pad_owned=False, pitch_owned=False):
     """One hop ``S @ x`` (torch.spmm(adj, x), utils.py:95).  Returns a new [n_rows, F] fp32
     tensor.  With ``mean``/``std`` (fp32 [F]) the gathered operand is standardised on the fly.
     ``out``: optional [n_rows, F] fp32 destination (any row stride >= F); only its columns [0, F) are
@@ -197,7 +199,10 @@ def hop(adj, x, mean=None, std=None, chunk=None, slab=None, hints=None, std_mode
     lets the kernel finish every row with whole 16-byte stores.
     ``peers``: device addresses of other GPUs' buffers (same row 0 and leading dimension as ``out``)
     that receive every output row from the kernel's epilogue (row-sharded propagation, dist.py);
-    ``peer_mask`` (int32/uint32 [n_rows], optional): bit p set = row must go to peers[p]."""
+    ``peer_mask`` (int32/uint32 [n_rows], optional): bit p set = row must go to peers[p].
+    ``pitch_owned=True`` (implies ``pad_owned``) declares ALL columns from F to the row stride of ``out`` and of
+    every peer buffer to be padding -- whole padded rows, not column views; only then are consecutive rows sent
+    to the peers as one store per tile, which zero-fills those columns there (SGC_HOP_PITCH_OWNED)."""
     g = as_graph(adj)
     dev = require_cuda(g.device)
     x = _check_features(g, x)
@@ -219,7 +224,7 @@ def hop(adj, x, mean=None, std=None, chunk=None, slab=None, hints=None, std_mode
         partial = _partial(plan, f, dev)
         a = _hop_args(g, plan, x.data_ptr(), x.stride(0), y.data_ptr(), y.stride(0), f, partial, mean, std,
                       std_mode or default_std_mode(), default_slab() if slab is None else slab,
-                      default_hints() if hints is None else hints, peers, peer_mask, pad_owned)
+                      default_hints() if hints is None else hints, peers, peer_mask, pad_owned, pitch_owned)
         _ffi.call("sgc_spmm_hop", plan.handle, _ffi.ctypes.byref(a), stream_ptr())
     return y
 

@@ -96,17 +96,29 @@ def test_hop_pushes_rows_to_peer_buffers():
         bufs = [torch.full((n + 3, ld), -7.0, device=dev) for _ in range(3)]
         own, peers = bufs[0], bufs[1:]
         sgc_b200.hop(g, x, chunk=64, out=own[2:2 + n, :f], peers=[p[2:].data_ptr() for p in peers], pad_owned=True)
+        r4 = (f + 3) // 4 * 4
         for b in bufs:
             assert torch.equal(b[2:2 + n, :f], want), (f, tile_rows)
             assert bool((b[:2] == -7.0).all()) and bool((b[2 + n:] == -7.0).all())
-            pad = b[2:2 + n, f:]                  # pad columns: untouched, or zero-filled by the bulk store
+            # pad_owned hands over [f, round4(f)) only: everything beyond keeps its value, here and on the peers
+            assert bool((b[2:2 + n, r4:] == -7.0).all()), (f, tile_rows)
+            pad = b[2:2 + n, f:r4]
+            assert bool(((pad == -7.0) | (pad == 0.0)).all())
+        # pitch_owned: whole padded rows -- tiles of consecutive rows may leave as one store, zero-filling [f, ld)
+        bufs = [torch.full((n + 3, ld), -7.0, device=dev) for _ in range(3)]
+        sgc_b200.hop(g, x, chunk=64, out=bufs[0][2:2 + n, :f], peers=[p[2:].data_ptr() for p in bufs[1:]],
+                     pitch_owned=True)
+        for b in bufs:
+            assert torch.equal(b[2:2 + n, :f], want), (f, tile_rows)
+            assert bool((b[:2] == -7.0).all()) and bool((b[2 + n:] == -7.0).all())
+            pad = b[2:2 + n, f:]
             assert bool(((pad == -7.0) | (pad == 0.0)).all())
         # halo mask: a row reaches peer p only if bit p of its mask is set
         mask = torch.randint(0, 4, (n,), dtype=torch.int32, device=dev)
         mask[: n // 3] = 3                        # long runs of rows every peer needs: the tile-store path
         bufs = [torch.full((n + 3, ld), -7.0, device=dev) for _ in range(3)]
         sgc_b200.hop(g, x, chunk=64, out=bufs[0][2:2 + n, :f], peers=[p[2:].data_ptr() for p in bufs[1:]],
-                     peer_mask=mask, pad_owned=True)
+                     peer_mask=mask, pitch_owned=True)
         assert torch.equal(bufs[0][2:2 + n, :f], want)
         for slot, b in enumerate(bufs[1:]):
             sent = ((mask >> slot) & 1).bool()
@@ -125,6 +137,31 @@ def test_hop_pushes_rows_to_peer_buffers():
     bufs = [torch.zeros((n, 136), device=dev) for _ in range(2)]
     with pytest.raises(sgc_b200._ffi.SgcError):
         sgc_b200.hop(g, x, out=bufs[0][:, :130], peers=[bufs[1].data_ptr()])
+
+
+def test_peer_push_into_column_views_leaves_neighbours_alone():
+    """Without pitch_owned the peers' buffers may be column views of wider live matrices, exactly like `out`:
+    a narrow width on a pitch that fits one feature slab (the shape where tiles of rows would otherwise travel
+    as one store of rows*ld floats) must leave every neighbouring column on every peer untouched."""
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    import sgc_b200
+    from sgc_b200 import synth
+    dev = torch.device("cuda", 0)
+    s = synth.make_shape("reddit", device=dev, scale=0.02, seed=7)
+    n = s["n"]
+    g = sgc_b200.normalize_csr(n, s["row_ptr"], s["col"], s["val"])
+    for f, ld, c0, pad_owned in ((64, 128, 8, False), (100, 104, 0, False), (100, 104, 0, True), (30, 64, 4, True)):
+        x = s["x"][:, :f].contiguous()
+        want = sgc_b200.hop(g, x, chunk=64)
+        bufs = [torch.full((n + 2, ld), 9.0, device=dev) for _ in range(3)]
+        views = [b[1:1 + n, c0:c0 + f] for b in bufs]
+        sgc_b200.hop(g, x, chunk=64, out=views[0], peers=[v.data_ptr() for v in views[1:]], pad_owned=pad_owned)
+        keep = c0 + ((f + 3) // 4 * 4 if pad_owned else f)
+        for b in bufs:
+            assert torch.equal(b[1:1 + n, c0:c0 + f], want), (f, ld, c0)
+            assert bool((b[:, :c0] == 9.0).all()) and bool((b[:, keep:] == 9.0).all()), (f, ld, c0)
+            assert bool((b[0] == 9.0).all()) and bool((b[1 + n] == 9.0).all())
 
 
 def monkey_env(key, value):

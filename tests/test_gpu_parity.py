@@ -283,6 +283,69 @@ def test_column_blocked_hop(dev, monkeypatch, f):
     assert sgc_b200.propagate.col_blocks_for(graph, 416) == 0
 
 
+def test_hops_on_one_plan_from_two_streams(dev):
+    """Two ticket-scheduled hops on the SAME cached plan, in flight at once on different streams, draw their
+    tickets from different counter pairs (the counters used to be shared): both results are the
+    single-stream result, repeatedly, and later launches still start from clean counters."""
+    import sgc_b200
+    from sgc_b200 import _ffi
+    s, graph = powerlaw_case(dev, scale=0.05, seed=29)
+    h = _ffi_hints_force_tickets()
+    xa = s["x"][:, :128].contiguous()
+    xb = (s["x"][:, :128] * 0.5 + 1.0).contiguous()
+    want_a = sgc_b200.hop(graph, xa, chunk=0, hints=h)
+    want_b = sgc_b200.hop(graph, xb, chunk=0, hints=h)
+    sa, sb = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+    outs = [(torch.empty_like(want_a), torch.empty_like(want_b)) for _ in range(6)]
+    torch.cuda.synchronize(dev)
+    for ya, yb in outs:
+        with torch.cuda.stream(sa):
+            sgc_b200.hop(graph, xa, chunk=0, hints=h, out=ya)
+        with torch.cuda.stream(sb):
+            sgc_b200.hop(graph, xb, chunk=0, hints=h, out=yb)
+    torch.cuda.synchronize(dev)
+    for ya, yb in outs:
+        assert torch.equal(ya, want_a) and torch.equal(yb, want_b)
+    assert torch.equal(sgc_b200.hop(graph, xa, chunk=0, hints=h), want_a)
+
+
+def _ffi_hints_force_tickets():
+    from sgc_b200.propagate import default_hints
+    return default_hints() | 256                  # hints bit 8: ticket grid whatever the task count
+
+
+def test_column_blocks_of_row_slice_views(dev, monkeypatch):
+    """Row-slice views share the parent's `col` array and keep absolute offsets in `row_ptr` (pipeline.row_blocks,
+    the sharded propagator's sub-graphs).  With SGC_B200_COL_BLOCKS set, hop() takes the column-blocked path for
+    them too: their blocks must be built from the view's own entries only -- block by block the
+    entries tile [row_ptr[0], row_ptr[-1]), the hop equals the matching rows of the single-pass hop bit for bit,
+    and precompute_host(out_blocks > 1) gives the same bytes with and without column blocks."""
+    import sgc_b200
+    from sgc_b200.pipeline import row_blocks
+    s, graph = powerlaw_case(dev, scale=0.02, seed=23)
+    n = graph.n_rows
+    x = s["x"][:, :72].contiguous()
+    monkeypatch.setenv("SGC_B200_COL_BLOCKS", "0")
+    plain = sgc_b200.hop(graph, x, chunk=0)
+    views = row_blocks(graph, 5)
+    assert len(views) > 2
+    for r0, r1, sub in views:
+        b, e = int(sub.row_ptr[0]), int(sub.row_ptr[-1])
+        for nb in (2, 4):
+            blocks = sub.col_blocks(nb)
+            assert sum(g.nnz for _, _, g in blocks) == e - b
+            assert all(int(g.row_ptr[0]) == 0 and int(g.row_ptr[-1]) == g.nnz for _, _, g in blocks)
+        monkeypatch.setenv("SGC_B200_COL_BLOCKS", "3")
+        assert torch.equal(sgc_b200.hop(sub, x, chunk=0), plain[r0:r1]), (r0, r1)
+        monkeypatch.setenv("SGC_B200_COL_BLOCKS", "0")
+    host = (n, s["row_ptr"].cpu().pin_memory(), s["col"].cpu().pin_memory(), s["val"].cpu().pin_memory())
+    x_host = x.cpu().pin_memory()
+    want = sgc_b200.precompute_host(host, x_host, 2, out_blocks=4, chunk=0, col_slab=0).clone()
+    monkeypatch.setenv("SGC_B200_COL_BLOCKS", "3")
+    got = sgc_b200.precompute_host(host, x_host, 2, out_blocks=4, chunk=0, col_slab=0)
+    assert torch.equal(got, want)
+
+
 def test_fused_norm_mode_is_bit_identical(dev, monkeypatch):
     """SGC_B200_FUSED_NORM=1 (weights formed in the kernel from fp64 A+I values and D^-1/2; S is
     never materialised) and the default (fp32 S values written once by sgc_norm_values at

@@ -53,7 +53,7 @@ src, dstb = prop.buf[0], prop.symm[1]
 out = dstb.tensor[row0:row1, :f]
 peers = dstb.row_ptrs(row0, peers_only=True)
 h = default_hints()
-kw = dict(out=out, peers=peers, peer_mask=prop.peer_mask, pad_owned=True)
+kw = dict(out=out, peers=peers, peer_mask=prop.peer_mask, pad_owned=True, pitch_owned=True)
 report("plain kernel, no peers (last hop)", *timeit(lambda: hop(sg.graph, src[:, :f], out=out, pad_owned=True)), push=False)
 report("peer variant, pushes skipped (hints 8)", *timeit(lambda: hop(sg.graph, src[:, :f], hints=h | 8, **kw)), push=False)
 for rows in (1, 2, 4, 8, 16, 32):

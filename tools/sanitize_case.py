@@ -38,12 +38,12 @@ for f in (100, 130, 602, 7):
         os.environ["SGC_B200_PUSH_ROWS"] = str(rows_per_tile)
         bufs = [torch.full((n + 3, ld), -7.0, device=dev) for _ in range(3)]
         sgc_b200.hop(gr, xs, chunk=64, out=bufs[0][2:2 + n, :f], peers=[p[2:].data_ptr() for p in bufs[1:]],
-                     pad_owned=True)
+                     pad_owned=True, pitch_owned=True)
         assert all(torch.equal(b[2:2 + n, :f], want) for b in bufs), (f, rows_per_tile)
         mask = torch.randint(0, 4, (n,), dtype=torch.int32, device=dev)
         bufs = [torch.full((n + 3, ld), -7.0, device=dev) for _ in range(3)]
         sgc_b200.hop(gr, xs, chunk=64, out=bufs[0][2:2 + n, :f], peers=[p[2:].data_ptr() for p in bufs[1:]],
-                     peer_mask=mask, pad_owned=True)
+                     peer_mask=mask, pad_owned=True, pitch_owned=True)
         for slot, b in enumerate(bufs[1:]):
             sent = ((mask >> slot) & 1).bool()
             assert torch.equal(b[2:2 + n, :f][sent], want[sent]) and bool((b[2:2 + n][~sent] == -7.0).all())

@@ -23,7 +23,7 @@ for p_rows in (2, 4, 8):
     line = "products 1/%d rows, %d stand-in peers: plain %.3f" % (p_rows, p_rows - 1, t_ms(lambda: sgc_b200.hop(sub, x, out=o, pad_owned=True)))
     for rows in ("1", "2", "4", "8"):
         os.environ["SGC_B200_PUSH_ROWS"] = rows
-        line += " | tile %s: no push %.3f pushing %.3f" % (rows, t_ms(lambda: sgc_b200.hop(sub, x, out=o, peers=pp, pad_owned=True, hints=H | 8)),
-                                                            t_ms(lambda: sgc_b200.hop(sub, x, out=o, peers=pp, pad_owned=True)))
+        line += " | tile %s: no push %.3f pushing %.3f" % (rows, t_ms(lambda: sgc_b200.hop(sub, x, out=o, peers=pp, pad_owned=True, pitch_owned=True, hints=H | 8)),
+                                                            t_ms(lambda: sgc_b200.hop(sub, x, out=o, peers=pp, pad_owned=True, pitch_owned=True)))
     print(line, flush=True)
     del peers, own, sub; torch.cuda.empty_cache()
