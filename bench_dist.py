@@ -456,6 +456,53 @@ def extra_record(x, world, B):
     return rec
 
 
+def weak_scaling_reference(name, world, lam, dev, B):
+    """SURVEY 8(e)'s yardstick for a workload no single GPU can hold (papers100M shape): the SAME generator at
+    1/world of the size -- nodes and pairs scaled together, same degree law, same feature width and K -- run on ONE
+    GPU of this box with the single-GPU hop kernel, device-timed like every other single-GPU leg.  The caller
+    reports  weak_scaling_efficiency = rate(world GPUs, full size) / (world * rate(1 GPU, 1/world size)),
+    rate = K * nnz(S) * F / step time.  Rank 0 only; no collective inside."""
+    synth = B["load_synth"]()
+    shape = synth.SHAPES[name]
+    t0 = time.perf_counter()
+    s = synth.make_shape(name, device=dev, scale=1.0 / world, lam=lam, with_features=False)
+    n1, f, k = s["n"], shape["f"], shape["k"]
+    x = synth.gaussian_features(n1, f, seed=1, scaled=False, device=dev)
+    single, y = _single_gpu_reference(s, x, n1, f, k)
+    del y, s, x
+    torch.cuda.empty_cache()
+    single.update({"n": n1, "f": f, "k": k, "nnz_S": int(round(single["value"] * single["ms_per_step"] * 1e-3 / (k * f))),
+                   "generator_scale": 1.0 / world, "partition_locality_lambda": lam,
+                   "wall_s": time.perf_counter() - t0,
+                   "what": "the same generator at 1/%d size (nodes and pairs scaled together) on ONE GPU, K hops on "
+                           "device-resident inputs, CUDA events, median-free mean of 5 steps after 3 warm-ups" % world})
+    return single
+
+
+def _r3(v):
+    return None if v is None else float("%.3g" % v)
+
+
+def summary_of(name, line, extras):
+    """Compact digest of every leg of this run -- {leg: {ms, eff, par}} -- kept under 600 characters and placed at
+    the very end of the JSON line, so that a reader who only has the last 1500 characters of the output still
+    sees every leg's step time, efficiency (strong scaling against one GPU of this box, null where no single-GPU
+    run of the leg exists) and whether its result check passed."""
+    out = {name: {"ms": _r3(line["ms_per_step"]), "eff": _r3(line["strong_scaling_efficiency"]),
+                  "par": line["parity"].get(name)}}
+    for key, v in extras.items():
+        if not isinstance(v, dict):
+            continue
+        if "ms_per_step" in v:
+            eff = v.get("strong_scaling_efficiency")
+            if eff is None:
+                eff = v.get("weak_scaling_efficiency")
+            out[key] = {"ms": _r3(v["ms_per_step"]), "eff": _r3(eff), "par": (v.get("parity") or {}).get("ok")}
+        else:
+            out[key] = {"skip": str(v.get("skipped") or v.get("error") or "?")[:40]}
+    return out
+
+
 def bench(args, rank, world, dev, B):
     name = args.workload
     failed = []
@@ -488,6 +535,19 @@ def bench(args, rank, world, dev, B):
                 extras[key] = extra_record(x, world, B)
                 if x["parity"] is not None and not x["parity"]["ok"]:
                     failed.append(key)
+                if x["single"] is None and rank == 0 and os.environ.get("SGC_BENCH_WEAK_REF", "1") == "1":
+                    # no one-GPU run of this size exists: weak scaling against the 1/world-size generator (8e)
+                    del x
+                    torch.cuda.empty_cache()
+                    try:
+                        ref = weak_scaling_reference(other, world, lam, dev, B)
+                        extras[key]["weak_scaling_reference"] = ref
+                        extras[key]["weak_scaling_efficiency"] = extras[key]["value"] / (world * ref["value"])
+                        extras[key]["weak_scaling_efficiency_is"] = (
+                            "rate(%d GPUs, full size) / (%d x rate(1 GPU, 1/%d-size graph of the same generator)), "
+                            "rate = K*nnz(S)*F / step time (SURVEY 8e)" % (world, world, world))
+                    except Exception as exc:
+                        extras[key]["weak_scaling_reference"] = {"error": repr(exc)[:300]}
             except Exception as exc:            # an optional extra must never cost the primary line
                 extras[key] = {"error": repr(exc)[:400]}
                 torch.cuda.empty_cache()
@@ -506,11 +566,17 @@ def bench(args, rank, world, dev, B):
             "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": B["workload_config"](name, n, nnz, f, k),
-            "roofline": {"bound": "l2" if (r["mode"] == "features" or n * 128 * 4 <= 128 * 1024 * 1024) else "hbm", "achieved": achieved, "peak": peak,
+            # one yardstick, stated: SURVEY 8(d)'s gather-model bytes against the measured HBM copy figure.  A
+            # fraction above 1 is not a faster-than-HBM kernel: it is the share of the gathers that L2 served
+            # (Reddit slabs are L2-resident; the N=1 line carries the L2 -> SM probe and the ncu DRAM bytes)
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak,
                          "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                         "achieved_is": "gather-model bytes per GPU / step time (multi-GPU kernels are not run under "
-                                        "ncu); peak is the measured HBM copy figure -- for the L2-resident Reddit slabs "
-                                        "the binding path is L2 -> SM, see the N=1 line's roofline.l2",
+                         "achieved_is": "gather-model (algorithmic) bytes per GPU / step time; multi-GPU kernels are "
+                                        "not run under ncu, so there is no DRAM counter here.  frac > 1 = re-reads of "
+                                        "L2-resident rows served by L2 instead of HBM, not skipped work (every leg is "
+                                        "verified); the hardware-counter view of this kernel is the N=1 line's "
+                                        "roofline.l2 / roofline.dram",
+                         "l2_resident_operand": bool(r["mode"] == "features" or n * 128 * 4 <= 128 * 1024 * 1024),
                          "kernel": "spmm_hop_kernel (per GPU)"},
             "cpu_baseline": None, "e2e": r["e2e"], "gpu_launches": r["launches"], "clocks": r["clocks"],
             "parity": {name: (r["parity"]["ok"] if r["parity"] else None),
@@ -527,6 +593,7 @@ def bench(args, rank, world, dev, B):
             "strong_scaling_efficiency": (r["value"] / (world * r["single"]["value"]) if r["single"] else None),
             "other_workloads": extras,
         }
+        line["summary"] = summary_of(name, line, extras)      # LAST key: survives a tail-truncated log
         print(json.dumps(line), flush=True)
     dist.barrier()
     dist.destroy_process_group()

@@ -410,6 +410,40 @@ def test_fused_standardisation(dev):
     assert torch.equal(y3, y2)
 
 
+def test_standardised_path_is_no_further_from_fp64_than_the_reference(dev):
+    """The path that ships for Reddit (K3 statistics on the GPU -> exact in-place (x-mean)/std -> K hops) against
+    the exact answer: utils.py:118-119 and the hops of utils.py:94-95 evaluated in fp64 on the CPU with the same
+    fp32 S values.  The reference's own fp32 evaluation (torch mean/std/spmm on the CPU -- its literal
+    expressions) differs from the GPU's on a fraction of the elements because its fp32 column statistics carry
+    rounding noise; the bar is accuracy: on EVERY element |gpu - fp64| <= |reference - fp64| + 1e-6 + 1e-5*|fp64|
+    (north_star's tolerance), through load-time standardisation and through precompute_host alike."""
+    import sgc_b200
+    s, graph = powerlaw_case(dev, scale=0.03, seed=41)
+    n, k = s["n"], 2
+    x_raw = s["x"][:, :200].contiguous()
+    xh = x_raw.cpu()
+    sv = graph.values32().cpu()
+    idx = torch.stack([torch.from_numpy(coo_rows(graph)), graph.col.cpu().long()])
+    adj32 = torch.sparse_coo_tensor(idx, sv, (n, n))
+    ref = (xh - xh.mean(dim=0)) / xh.std(dim=0)                       # utils.py:119, verbatim
+    truth = (xh.double() - xh.double().mean(dim=0)) / xh.double().std(dim=0)
+    adj64 = adj32.to(torch.float64)
+    for _ in range(k):
+        ref = torch.spmm(adj32, ref)                                   # utils.py:95
+        truth = torch.spmm(adj64, truth)
+    mean, std = sgc_b200.col_stats(x_raw)
+    feats = sgc_b200.StandardizedFeatures(sgc_b200.to_padded(x_raw.clone()), mean, std)
+    got, _ = sgc_b200.sgc_precompute(feats, graph, k)
+    host = (n, s["row_ptr"].cpu().pin_memory(), s["col"].cpu().pin_memory(), s["val"].cpu().pin_memory())
+    got_host = sgc_b200.precompute_host(host, xh.pin_memory(), k, standardize=True)
+    for y in (got.cpu(), got_host):
+        e_gpu = (y.double() - truth).abs()
+        e_ref = (ref.double() - truth).abs()
+        bad = e_gpu > e_ref + ATOL + RTOL * truth.abs()
+        assert int(bad.sum()) == 0, (int(bad.sum()), float(e_gpu.max()), float(e_ref.max()))
+        assert float(e_gpu.mean()) <= float(e_ref.mean()) * 1.05 + 1e-9   # and not worse on average either
+
+
 @pytest.mark.parametrize("blocks,col_slab", [(1, None), (3, None), (8, None), (1, 32), (1, 64)])
 def test_precompute_host_pipeline(dev, blocks, col_slab):
     """Host-to-host entry point (pipeline.precompute_host: overlapped H2D; column-slab pipeline or

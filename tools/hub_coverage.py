@@ -29,6 +29,15 @@ srt, _ = torch.sort(cnt, descending=True)
 cum = torch.cumsum(srt, 0).double() / nnz
 print("workload %s: N = %d, nnz(S) = %d, max gather count = %d, mean = %.1f" % (name, n, nnz, int(srt[0]), nnz / n))
 print("%8s %10s %14s %s" % ("H rows", "coverage", "min count", "smem for a 128-float slab piece (512 B/row)"))
+# L2 budgets: how many whole padded rows of X fit, and the share of all gathers they would serve if exactly the
+# most-gathered rows stayed resident (the ceiling of any hot-set / residency scheme)
+f = synth.SHAPES[name]["f"]
+row_bytes = (f + 7) // 8 * 8 * 4
+print("L2 residency ceiling, whole rows of %d bytes:" % row_bytes)
+for mb in (16, 32, 48, 64, 96, 126):
+    h = min(n, mb * (1 << 20) // row_bytes)
+    print("  %4d MB = %8d rows (%5.2f %% of N): %5.1f %% of the gathers, min count %d" % (
+        mb, h, 100.0 * h / n, 100 * cum[h - 1].item(), int(srt[h - 1])))
 for h in (128, 256, 384, 400, 512, 768, 1024, 1600, 2048, 3200, 4096, 8192, 16384, 32768):
     if h <= n:
         print("%8d %9.1f%% %14d %8.0f KB" % (h, 100 * cum[h - 1].item(), int(srt[h - 1]), h * 512 / 1024))
