@@ -74,17 +74,30 @@ def ncu_traffic(workload):
     return None
 
 
-def capture_matches_build():
-    """True when the libsgc_b200.so being timed is byte for byte the one the committed ncu captures profiled
-    (profiles/roofline_traffic.json `build_sha256`), False when it differs, None when no hash was recorded."""
+def kernel_source_sha256():
+    """sha256 over the kernel sources the library is built from (sgc_b200/csrc/*.cu, *.cuh, Makefile, in name
+    order).  The sources, not the .so: nvcc's output is not byte-reproducible from one build to the next."""
+    import glob
     import hashlib
+    h = hashlib.sha256()
+    base = os.path.join(ROOT, "sgc_b200", "csrc")
+    for path in sorted(glob.glob(os.path.join(base, "*.cu")) + glob.glob(os.path.join(base, "*.cuh"))
+                       + [os.path.join(base, "Makefile")]):
+        h.update(os.path.basename(path).encode() + b"\0")
+        with open(path, "rb") as fh:
+            h.update(fh.read())
+    return h.hexdigest()
+
+
+def capture_matches_build():
+    """True when the kernel sources of the library being timed are the ones the committed ncu captures were
+    taken from (profiles/roofline_traffic.json `source_sha256`), False when they differ, None when no hash was
+    recorded."""
     path = os.path.join(ROOT, "profiles", "roofline_traffic.json")
     try:
         with open(path) as fh:
-            want = json.load(fh).get("build_sha256")
-        from sgc_b200 import _ffi
-        with open(_ffi.LIB_PATH, "rb") as fh:
-            got = hashlib.sha256(fh.read()).hexdigest()
+            want = json.load(fh).get("source_sha256")
+        got = kernel_source_sha256()
     except Exception:
         return None
     return None if not want else (got == want)

@@ -1,15 +1,20 @@
 """Turns the selected ncu CSVs of one hop launch per shape (tools/ncu_select.py output) into
 profiles/roofline_traffic.json, the per-launch hardware counters bench.py's `roofline` block reads.
 
-    python tools/ncu_to_traffic.py <build sha256> reddit=profiles/r03_ncu_full_spmm_hop_reddit.csv products=... > profiles/roofline_traffic.json
+    python tools/ncu_to_traffic.py <sha256 of the profiled .so> reddit=profiles/r03_ncu_full_spmm_hop_reddit.csv products=... > profiles/roofline_traffic.json
 
 Every figure is per launch of the hop kernel as captured by `ncu --set full --clock-control none`; `build_sha256` is
-the sha256 of the libsgc_b200.so that was profiled, so that bench.py can say whether the library it times is the
-one the counters describe."""
+the sha256 of the libsgc_b200.so that was profiled (a record: nvcc output is not byte-reproducible), `source_sha256`
+that of the kernel sources it was built from (bench.kernel_source_sha256), which bench.py compares with the
+sources of the library it times."""
 import csv
 import datetime
 import json
+import os
 import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from bench import kernel_source_sha256  # noqa: E402
 
 UNIT_SCALE = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12, "ms": 1, "us": 1e-3, "s": 1e3,
               "msecond": 1, "usecond": 1e-3, "second": 1e3}
@@ -66,9 +71,9 @@ def entry(path):
 sha = sys.argv[1]
 out = {"_note": "per-launch counters of the hop kernel from `ncu --set full --clock-control none` captures "
                 "(tools/gpu_r3_evidence.sh, 1x B200); bench.py reads dram_bytes into roofline.traffic / roofline.dram, "
-                "the pipe percentages into roofline.hw_counters / roofline.bound, and compares build_sha256 with the "
-                "library it times",
-       "build_sha256": sha}
+                "the pipe percentages into roofline.hw_counters / roofline.bound, and compares source_sha256 with the "
+                "kernel sources of the library it times",
+       "build_sha256": sha, "source_sha256": kernel_source_sha256()}
 for arg in sys.argv[2:]:
     name, path = arg.split("=", 1)
     out[name] = entry(path)
